@@ -1,0 +1,289 @@
+/*
+ * taylorb200.h -- C ABI of libtaylorb200.so
+ *
+ * B200-native (sm_100a) replacement for the ensemble hot path of
+ * TaylorIntegration.jl: the `taylorinteg` / `taylorstep!` driver loop run over
+ * N independent trajectories.  Plain pointers and sizes only; no torch types.
+ *
+ * The reference has no FFI: its seam is Julia multiple dispatch.  Every entry
+ * point below names the reference method(s) it stands in for (paths relative
+ * to the TaylorIntegration.jl source tree, v0.18.14):
+ *
+ *   tb_ode_create        <- what `@taylorize` emits: the body of
+ *                           `jetcoeffs!(::Val{f}, t, x, dx, params, rv)`
+ *                           src/parse_eqs.jl:236-358 (skeleton 259-264),
+ *                           one TaylorSeries.<op>!(res, a, b, ord) call per
+ *                           tape entry (parse_eqs.jl:963-1135)
+ *   tb_compile           <- `_determine_parsing!` + `_allocate_jetcoeffs!`
+ *                           src/integrator/jetcoeffs.jl:147-192,
+ *                           src/parse_eqs.jl:138-181
+ *   tb_integrate*        <- `taylorinteg!(dense, f!, q0, t0, tmax, abstol,
+ *                           cache, params; ...)`
+ *                           src/integrator/taylorinteg.jl:329-381   (t0,tmax)
+ *                           src/integrator/taylorinteg.jl:582-642   (trange)
+ *                           src/rootfinding.jl:347-438              (events)
+ *                           src/lyapunovspectrum.jl:340-429         (Lyapunov)
+ *                           batched over the trajectory index.
+ *   tb_jet               <- one `taylorstep!` src/integrator/taylorstep.jl:59-82
+ *                           (jets + step size of the first step; parity probe)
+ *   tb_dense_eval        <- `(sol::TaylorSolution)(t)`
+ *                           src/integrator/taylorsolution.jl:337-423
+ *
+ * Layout convention: every per-trajectory array is structure-of-arrays with
+ * the trajectory index fastest, i.e. element (component c, trajectory i) of a
+ * `[dof x N]` array lives at `c*N + i`.
+ *
+ * Error convention: functions return 0 on success and a negative tb_status on
+ * API / compile / launch failure (message through tb_last_error()).
+ * Integration-level conditions never fail the call: they are reported per
+ * trajectory in `status[i]` as TB_ST_* bit flags mirroring the reference's
+ * warnings.
+ */
+#ifndef TAYLORB200_H
+#define TAYLORB200_H
+
+#include <stdint.h>
+#include <stddef.h>
+
+#ifdef __cplusplus
+extern "C" {
+#endif
+
+#define TB_ABI_VERSION 1
+
+/* ---- return codes -------------------------------------------------------- */
+enum tb_status {
+    TB_OK = 0,
+    TB_ERR_ARG = -1,      /* bad argument / malformed tape                   */
+    TB_ERR_COMPILE = -2,  /* NVRTC failed (log in tb_last_error)             */
+    TB_ERR_CUDA = -3,     /* CUDA runtime error or no usable device          */
+    TB_ERR_UNSUPPORTED = -4
+};
+
+/* ---- per-trajectory status bits ------------------------------------------ */
+#define TB_ST_OK 0
+#define TB_ST_MAXSTEPS 1   /* "Maximum number of integration steps reached"  taylorinteg.jl:372-377 */
+#define TB_ST_ZERO_STEP 2  /* "The step-size is zero; aborting integration." taylorinteg.jl:360-363 */
+#define TB_ST_NR_NOCONV 4  /* "Newton-Raphson did not converge ..."          rootfinding.jl:222-224 */
+#define TB_ST_NONFINITE 8  /* state became NaN/Inf (no reference analogue; the reference would loop) */
+#define TB_ST_EVENT_OVERFLOW 16 /* more events than `event_capacity`        */
+
+/* ---- tape ----------------------------------------------------------------
+ * One entry = one `TaylorSeries.<op>!(res, a, b, ord)` call in the body of the
+ * generated `for ord = 0:order-1` loop (parse_eqs.jl:259-264).
+ */
+enum tb_opcode {
+    TB_OP_NOP = 0,
+    TB_OP_IDENTITY = 1, /* identity!(res, a, k)                 res[k] = a[k]                 */
+    TB_OP_NEG = 2,      /* subst!(res, a, k)                    res[k] = -a[k]                */
+    TB_OP_ADD = 3,      /* add!(res, a, b, k)     (series|scalar) + (series|scalar)           */
+    TB_OP_SUB = 4,      /* subst!(res, a, b, k)                                                */
+    TB_OP_MUL = 5,      /* mul!(res, a, b, k)     Cauchy product, or scalar*series            */
+    TB_OP_DIV = 6,      /* div!(res, a, b, k)     series/series, series/scalar, scalar/series */
+    TB_OP_SQR = 7,      /* sqr!(res, a, k)        (what pow! dispatches to for ^2)            */
+    TB_OP_SQRT = 8,     /* sqrt!(res, a, k)                                                    */
+    TB_OP_POW = 9,      /* pow!(res, a, aux, imm, k)  constant real exponent in .imm          */
+    TB_OP_EXP = 10,     /* exp!(res, a, k)                                                     */
+    TB_OP_LOG = 11,     /* log!(res, a, k)                                                     */
+    TB_OP_SINCOS = 12,  /* sincos!(res, aux, a, k)    res = sin(a), aux = cos(a)              */
+    TB_OP_ZERO = 13,    /* zero!(res, a, k)                                                    */
+    TB_OP_ONE = 14,     /* one!(res, a, k)                                                     */
+    TB_OP_TAN = 15,     /* tan!(res, a, aux, k)       aux = tan(a)^2                          */
+    TB_OP_SINHCOSH = 16,/* sinhcosh!(res, aux, a, k)  res = sinh(a), aux = cosh(a)            */
+    TB_OP_TANH = 17,    /* tanh!(res, a, aux, k)      aux = tanh(a)^2                         */
+    TB_OP_ATAN = 18,    /* atan!(res, a, aux, k)      aux = 1 + a^2                           */
+    TB_OP_ASIN = 19,    /* asin!(res, a, aux, k)      aux = sqrt(1 - a^2)                     */
+    TB_OP_ACOS = 20,    /* acos!(res, a, aux, k)      aux = sqrt(1 - a^2)                     */
+    TB_OP__COUNT
+};
+
+/* operand = kind<<24 | index */
+enum tb_operand_kind {
+    TB_K_NONE = 0,
+    TB_K_X = 1,    /* x[index]   state jet                                   */
+    TB_K_DX = 2,   /* dx[index]  RHS jet                                     */
+    TB_K_TMP = 3,  /* temporary series (RetAlloc.v0, parse_eqs.jl:80-107)    */
+    TB_K_PAR = 4,  /* params[index], a plain number (`local mu = p`)         */
+    TB_K_TIME = 5, /* the independent variable t = [t0, 1, 0, ...]           */
+    TB_K_IMM = 6   /* numeric literal, value in tb_op_t.imm                  */
+};
+#define TB_OPERAND(kind, index) ((int32_t)(((uint32_t)(kind) << 24) | ((uint32_t)(index) & 0xFFFFFFu)))
+#define TB_OPERAND_KIND(o) ((int)(((uint32_t)(o)) >> 24))
+#define TB_OPERAND_INDEX(o) ((int)(((uint32_t)(o)) & 0xFFFFFFu))
+
+typedef struct tb_op {
+    int32_t op;   /* tb_opcode                                               */
+    int32_t res;  /* result operand (TB_K_DX or TB_K_TMP)                    */
+    int32_t a;    /* first argument                                          */
+    int32_t b;    /* second argument or TB_K_NONE                            */
+    int32_t aux;  /* auxiliary series (pow!, sincos!, ...) or TB_K_NONE      */
+    int32_t flags;
+    double imm;   /* literal operand or pow! exponent                        */
+} tb_op_t;
+
+/* Jacobian entry for Lyapunov spectra (stabilitymatrix!, lyapunovspectrum.jl:45-80).
+ * The order-1 TaylorN pass over the tape is done at tape-build time; each entry
+ * of the dof x dof Jacobian (row-major here: jac[i*dof + j] = d(dx_i)/d(x_j))
+ * is structurally zero, a constant series [c,0,0,...] or a series operand.    */
+enum tb_jac_kind { TB_JAC_ZERO = 0, TB_JAC_CONST = 1, TB_JAC_SERIES = 2 };
+typedef struct tb_jac_entry {
+    int32_t kind;    /* tb_jac_kind                                          */
+    int32_t operand; /* series operand when kind == TB_JAC_SERIES            */
+    double c;        /* constant when kind == TB_JAC_CONST                   */
+} tb_jac_entry_t;
+
+/* Event gate: the Bool of the `(Bool, Taylor1)` tuple returned by g
+ * (rootfinding.jl:124-132), restricted to a sign test on a constant term.    */
+enum tb_gate_cmp { TB_GATE_ALWAYS = 0, TB_GATE_GT0 = 1, TB_GATE_LT0 = 2, TB_GATE_GE0 = 3, TB_GATE_LE0 = 4 };
+
+typedef struct tb_ode_desc {
+    int32_t dof;      /* number of state components                          */
+    int32_t npar;     /* number of scalar parameters                         */
+    int32_t ntmp;     /* number of temporaries (all three tape segments)     */
+    int32_t nops;     /* RHS tape: ops[0 .. nops)                            */
+    int32_t ev_nops;  /* event tape: ops[nops .. nops+ev_nops)   (0 = none)  */
+    int32_t jac_nops; /* Jacobian tape: the next jac_nops ops    (0 = none)  */
+    const tb_op_t *ops;
+    int32_t ev_g;        /* operand holding the series of g                  */
+    int32_t ev_gate;     /* operand whose constant term gates the event      */
+    int32_t ev_gate_cmp; /* tb_gate_cmp                                      */
+    int32_t has_jac;     /* jac[] valid (dof*dof entries)                    */
+    const tb_jac_entry_t *jac;
+} tb_ode_desc_t;
+
+/* ---- compile options ----------------------------------------------------- */
+enum tb_mode {
+    TB_MODE_PARITY = 0, /* reference operation order, no FMA contraction,
+                           correctly rounded div/sqrt, shared deterministic
+                           pow/log/exp/sincos: bitwise equal to the oracle    */
+    TB_MODE_FAST = 1    /* FMA, re-associated sums, reciprocal multiplies     */
+};
+enum tb_kind {
+    TB_KIND_PLAIN = 0,  /* taylorinteg (t0,tmax) and trange                   */
+    TB_KIND_EVENTS = 1, /* + findroot!                                        */
+    TB_KIND_LYAP = 2    /* lyap_taylorinteg                                   */
+};
+
+typedef struct tb_compile_opts {
+    int32_t order;         /* Taylor order p (1..40)                          */
+    int32_t mode;          /* tb_mode                                         */
+    int32_t kind;          /* tb_kind                                         */
+    int32_t block_threads; /* 0 = default                                     */
+    int32_t reg_budget;    /* fast mode: doubles of jet storage kept in registers per trajectory (0 = default) */
+    int32_t min_blocks_per_sm; /* 0 = default                                 */
+    int32_t flags;         /* TB_CF_*                                         */
+    int32_t reserved;
+} tb_compile_opts_t;
+#define TB_CF_NO_DISK_CACHE 1 /* do not read/write the on-disk cubin cache    */
+#define TB_CF_KEEP_SOURCE 2   /* (always on) keep generated source for tb_get_source */
+
+/* ---- integration options: keyword arguments of taylorinteg -------------- */
+typedef struct tb_opts {
+    double abstol;       /* positional `abstol`                               */
+    double reltol;       /* reltol = 0               taylorinteg.jl:313-319   */
+    double minstepsize;  /* minstepsize = 0                                   */
+    double maxstepsize;  /* maxstepsize = Inf                                 */
+    int64_t maxsteps;    /* maxsteps = 500                                    */
+    int32_t eventorder;  /* eventorder = 0           rootfinding.jl:310-318   */
+    int32_t newtoniter;  /* newtoniter = 10                                   */
+    double nrabstol;     /* nrabstol = eps(Float64)                           */
+    int32_t event_capacity; /* events kept per trajectory (reference: maxsteps+1) */
+    int32_t params_per_traj; /* 1: params is [npar x N]; 0: params is [npar], shared */
+    int64_t steps_stride;  /* per-step outputs: columns per trajectory (>= maxsteps+1), 0 = maxsteps+1 */
+    int32_t sort_by_cost;  /* reserved                                        */
+    int32_t reserved;
+} tb_opts_t;
+
+/* ---- outputs (caller-owned; NULL = not requested) ------------------------
+ * Host pointers for tb_integrate, device pointers for tb_integrate_device.  */
+typedef struct tb_out {
+    double *xfinal;    /* [dof x N]   state at the end of the integration     */
+    double *tfinal;    /* [N]         time reached                            */
+    int64_t *nsteps;   /* [N]         steps taken (reference `nsteps - 1`)    */
+    int32_t *status;   /* [N]         TB_ST_* flags                           */
+    /* trange variant: taylorinteg.jl:582-642, NaN-prefilled cache.jl:313-316 */
+    double *xv_trange; /* [dof x nt x N]  element (c, j, i) at (c*nt + j)*N + i */
+    /* per-step storage, the reference's tv / xv (taylorinteg.jl:366-371)     */
+    double *tv;        /* [stride x N]      tv[s*N + i], s = 0..nsteps        */
+    double *xv;        /* [dof x stride x N]                                  */
+    double *psol;      /* [dof x (order+1) x stride x N] dense output, element
+                          (c, k, s, i) at ((c*(order+1) + k)*stride + s)*N + i */
+    /* events: rootfinding.jl:225-231                                         */
+    double *tevents;   /* [event_capacity x N]                                */
+    double *xevents;   /* [dof x event_capacity x N]                          */
+    double *gresids;   /* [event_capacity x N]                                */
+    int32_t *nevents;  /* [N]                                                 */
+    /* Lyapunov: lyapunovspectrum.jl:411-415                                  */
+    double *lambda;    /* [dof x N]   exponents at tfinal                     */
+    double *lambda_v;  /* [dof x stride x N] per step (with tv/xv), optional  */
+} tb_out_t;
+
+typedef struct tb_ode tb_ode_t;       /* validated tape                       */
+typedef struct tb_kernel tb_kernel_t; /* compiled kernel (immutable, shareable) */
+
+/* ---- entry points -------------------------------------------------------- */
+int tb_abi_version(void);
+const char *tb_last_error(void);
+
+/* copies the description; validates operand kinds/indices and op arity      */
+tb_ode_t *tb_ode_create(const tb_ode_desc_t *desc);
+void tb_ode_free(tb_ode_t *ode);
+
+/* default-initialise option structs with the reference's defaults           */
+void tb_opts_default(tb_opts_t *o);
+void tb_compile_opts_default(tb_compile_opts_t *o);
+
+/* Generates CUDA C++ for the tape (works without a GPU). Returns a pointer
+ * owned by the library (valid until the next call on this thread).          */
+const char *tb_generate_source(const tb_ode_t *ode, const tb_compile_opts_t *co);
+
+/* NVRTC-compiles for sm_100a (works without a GPU: cubin only); the module
+ * is loaded lazily on first launch. `device` < 0 = current device.          */
+tb_kernel_t *tb_compile(const tb_ode_t *ode, const tb_compile_opts_t *co);
+void tb_kernel_free(tb_kernel_t *k);
+const char *tb_kernel_source(const tb_kernel_t *k);
+const char *tb_kernel_log(const tb_kernel_t *k);      /* NVRTC / ptxas -v log */
+int tb_kernel_info(const tb_kernel_t *k, int *regs, int *smem_bytes, int *local_bytes,
+                   int *block_threads, int *blocks_per_sm);
+/* size and bytes of the cubin (for offline cuobjdump)                        */
+const void *tb_kernel_cubin(const tb_kernel_t *k, size_t *nbytes);
+
+/* (t0,tmax) ensemble, HOST buffers: copies in, launches, copies out.
+ * q0 [dof x N]; params [npar x N] or [npar]; t0/tmax scalars.               */
+int tb_integrate(tb_kernel_t *k, int64_t N, const double *q0, const double *params,
+                 double t0, double tmax, const tb_opts_t *opts, tb_out_t *out);
+/* same with a sorted output grid trange[nt] shared by all trajectories      */
+int tb_integrate_trange(tb_kernel_t *k, int64_t N, const double *q0, const double *params,
+                        const double *trange, int64_t nt, const tb_opts_t *opts, tb_out_t *out);
+
+/* DEVICE buffers, asynchronous on `stream` (a cudaStream_t; NULL = default).
+ * `work` is a device int64 scratch of tb_work_bytes() bytes.                 */
+size_t tb_work_bytes(void);
+int tb_integrate_device(tb_kernel_t *k, int64_t N, const double *d_q0, const double *d_params,
+                        double t0, double tmax, const double *d_trange, int64_t nt,
+                        const tb_opts_t *opts, const tb_out_t *d_out, void *d_work, void *stream);
+/* launches issued so far by this library (all kernels), for bench accounting */
+int64_t tb_launch_count(void);
+
+/* First Taylor step of each trajectory: jets x[dof x (order+1) x N] (element
+ * (c,k,i) at (c*(order+1)+k)*N + i) and the step size dt[N]. Host buffers.   */
+int tb_jet(tb_kernel_t *k, int64_t N, const double *q0, const double *params, double t0,
+           const tb_opts_t *opts, double *xjet, double *dt);
+
+/* Dense-output evaluation sol(t): psol as written by tb_integrate (host),
+ * tq[nq] query times; xq [dof x nq x N]. Out-of-range queries give NaN.      */
+int tb_dense_eval(int64_t N, int32_t dof, int32_t order, int64_t stride, const double *tv,
+                  const double *psol, const int64_t *nsteps, const double *tq, int64_t nq, double *xq);
+
+/* FP64 roofline probe: register-only DFMA chains on the current device.
+ * Returns achieved TFLOP/s (2 flops per DFMA) over >= `seconds` of work.     */
+int tb_fp64_peak(double seconds, double *tflops, double *ms);
+
+/* device management helpers for hosts without a CUDA binding                 */
+int tb_device_count(void);
+int tb_set_device(int device);
+
+#ifdef __cplusplus
+}
+#endif
+#endif /* TAYLORB200_H */
