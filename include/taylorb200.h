@@ -125,11 +125,16 @@ typedef struct tb_op {
  * The order-1 TaylorN pass over the tape is done at tape-build time; each entry
  * of the dof x dof Jacobian (row-major here: jac[i*dof + j] = d(dx_i)/d(x_j))
  * is structurally zero, a constant series [c,0,0,...] or a series operand.    */
-enum tb_jac_kind { TB_JAC_ZERO = 0, TB_JAC_CONST = 1, TB_JAC_SERIES = 2 };
+enum tb_jac_kind {
+    TB_JAC_ZERO = 0,
+    TB_JAC_CONST = 1,  /* the constant series [c, 0, 0, ...]                  */
+    TB_JAC_SERIES = 2, /* a series operand                                    */
+    TB_JAC_PAR = 3     /* the constant series [c * params[index], 0, ...]; operand = TB_OPERAND(TB_K_PAR, index) */
+};
 typedef struct tb_jac_entry {
     int32_t kind;    /* tb_jac_kind                                          */
-    int32_t operand; /* series operand when kind == TB_JAC_SERIES            */
-    double c;        /* constant when kind == TB_JAC_CONST                   */
+    int32_t operand; /* series operand (TB_JAC_SERIES) or parameter (TB_JAC_PAR) */
+    double c;        /* constant (TB_JAC_CONST) or multiplier (TB_JAC_PAR)   */
 } tb_jac_entry_t;
 
 /* Event gate: the Bool of the `(Bool, Taylor1)` tuple returned by g

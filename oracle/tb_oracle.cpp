@@ -603,6 +603,7 @@ int integ_lyap(Work &w, const double *q0, double t0, double tmax, const tb_opts_
                 const tb_jac_entry_t &e = d->jac[i * dof + j];
                 for (int k = 0; k <= P; k++) J[k] = 0.0;
                 if (e.kind == TB_JAC_CONST) J[0] = e.c;
+                else if (e.kind == TB_JAC_PAR) J[0] = e.c * w.par[TB_OPERAND_INDEX(e.operand)];
                 else if (e.kind == TB_JAC_SERIES) {
                     const double *s = w.series(e.operand);
                     if (!s) return TB_ERR_ARG;

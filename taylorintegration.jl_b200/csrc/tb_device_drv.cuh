@@ -1,0 +1,464 @@
+/*
+ * tb_device_drv.cuh -- second half of the NVRTC translation unit: the fixed
+ * (tape-independent) part of the fused kernel.  One thread integrates one
+ * trajectory from t0 to tmax without leaving the SM: jet coefficients
+ * (generated code), step size, Horner evaluation, event location, Lyapunov
+ * QR, output stores, all in one launch.
+ *
+ * Every function cites the reference routine it restates (paths relative to
+ * the TaylorIntegration.jl tree).  In parity mode each floating-point
+ * operation below is the same IEEE operation, in the same order, as in
+ * oracle/tb_oracle.cpp.
+ */
+#ifndef TB_DEVICE_DRV_CUH
+#define TB_DEVICE_DRV_CUH
+
+/* evaluate(a::Taylor1, dt): Horner, s = a[P]; s = s*dt + a[k]  (TaylorSeries) */
+__device__ __forceinline__ double tb_horner(const double *__restrict__ smt, int slot, double dt) {
+    double s = S(slot, TB_P);
+#pragma unroll 4
+    for (int k = TB_P - 1; k >= 0; k--) s = A_(M_(s, dt), S(slot, k));
+    return s;
+}
+
+/* _stepsize: src/integrator/stepsize.jl:107-111   (eps/a)^(1/k) */
+__device__ __forceinline__ double tb_stepsize_k(double a, double eps, int k) {
+    double aux = D_(eps, a);
+    double kinv = D_(1.0, (double)k);
+    return tb_pow(aux, kinv);
+}
+
+/* stepsize(x::Taylor1, abs, rel): stepsize.jl:58-77 */
+__device__ __forceinline__ double tb_stepsize1(const double *__restrict__ smt, int slot, double abseps, double releps) {
+    double x0norm = fabs(S(slot, 0));
+    double h = TB_INF;
+#pragma unroll
+    for (int k = TB_P - 1; k <= TB_P; k++) {
+        double aux = fabs(S(slot, k));
+        if (aux == 0.0) continue;
+        double rel = M_(releps, x0norm);
+        double eps = (abseps >= rel) ? abseps : rel;
+        double h1 = tb_stepsize_k(aux, eps, k);
+        h = fmin(h, h1);
+    }
+    return h;
+}
+
+/* _second_stepsize: stepsize.jl:119-132 */
+__device__ __noinline__ double tb_second_stepsize(const double *__restrict__ smt, int slot) {
+    bool allzero = true;
+    for (int k = 0; k <= TB_P; k++)
+        if (S(slot, k) != 0.0) { allzero = false; break; }
+    if (allzero) return TB_INF;
+    double h = 0.0;
+    for (int k = 1; k <= TB_P - 2; k++) {
+        double aux = fabs(S(slot, k));
+        if (aux == 0.0) continue;
+        h = fmax(h, tb_stepsize_k(aux, 1.0, k));
+    }
+    return h;
+}
+
+/* stepsize(q::AbstractArray{Taylor1}, abs, rel): stepsize.jl:79-99, then the
+ * clamp of taylorstep! (src/integrator/taylorstep.jl:79).  Only the first
+ * TB_DOF jets enter (lyap_taylorstep!, lyapunovspectrum.jl:270).             */
+__device__ __forceinline__ double tb_stepsize(const double *__restrict__ smt, const TbArgs &a) {
+    double h = TB_INF;
+#pragma unroll
+    for (int i = 0; i < TB_DOF; i++) h = fmin(h, tb_stepsize1(smt, i, a.abstol, a.reltol));
+    if (h == TB_INF) {
+        h = 0.0;
+        for (int i = 0; i < TB_DOF; i++) h = fmax(h, tb_second_stepsize(smt, i));
+    }
+    /* clamp(h, lo, hi) */
+    h = (h < a.minstep) ? a.minstep : ((h > a.maxstep) ? a.maxstep : h);
+    return h;
+}
+
+/* jetcoeffs!(::Val{f}, t, x, dx, params, rv): skeleton src/parse_eqs.jl:259-264 */
+__device__ __forceinline__ void tb_jetcoeffs(double *__restrict__ smt, const double *par, double t0) {
+    tb_rhs_k0(smt, par, t0);
+#pragma unroll 1
+    for (int k = 1; k < TB_P; k++) tb_rhs_k(smt, par, t0, k);
+}
+
+#if TB_KIND == 2
+/* modifiedGS!(A, Q, R): src/lyapunovspectrum.jl:118-146, column-major n x n;
+ * dot and norm as left-to-right sums (oracle: modifiedGS).                    */
+__device__ __forceinline__ void tb_mgs(const double *A, double *Q, double *Rd) {
+    double v[TB_DOF];
+#pragma unroll
+    for (int j = 0; j < TB_DOF; j++) {
+#pragma unroll
+        for (int r = 0; r < TB_DOF; r++) v[r] = A[r + j * TB_DOF];
+#pragma unroll
+        for (int i = 0; i < TB_DOF; i++) {
+            if (i < j) {
+                double dot = M_(Q[0 + i * TB_DOF], v[0]);
+#pragma unroll
+                for (int r = 1; r < TB_DOF; r++) dot = A_(dot, M_(Q[r + i * TB_DOF], v[r]));
+#pragma unroll
+                for (int r = 0; r < TB_DOF; r++) v[r] = B_(v[r], M_(dot, Q[r + i * TB_DOF]));
+            }
+        }
+        double ss = M_(v[0], v[0]);
+#pragma unroll
+        for (int r = 1; r < TB_DOF; r++) ss = A_(ss, M_(v[r], v[r]));
+        double nrm = Q_(ss);
+        Rd[j] = nrm;
+#pragma unroll
+        for (int r = 0; r < TB_DOF; r++) Q[r + j * TB_DOF] = D_(v[r], nrm);
+    }
+}
+#endif
+
+#if TB_KIND == 1
+/* coefficient k of derivative(g, eo) (repeated d[k] = (k+1) a[k+1], TaylorSeries) */
+__device__ __forceinline__ double tb_gder(const double *__restrict__ smt, int eo, int k) {
+    if (k + eo > TB_P) return 0.0;
+    double v = TB_EV_G(k + eo);
+    for (int r = eo; r >= 1; r--) v = M_((double)(k + r), v);
+    return v;
+}
+/* evaluate!(g_dg, dt): G = derivative(g, eo), dG = derivative(G), both Horner */
+__device__ __forceinline__ void tb_eval_g_dg(const double *__restrict__ smt, int eo, double dt, double *gv, double *dgv) {
+    double s = tb_gder(smt, eo, TB_P), ds = 0.0; /* dG[P] = 0 */
+    for (int k = TB_P - 1; k >= 0; k--) {
+        double Gk1 = tb_gder(smt, eo, k + 1);
+        ds = A_(M_(ds, dt), M_((double)(k + 1), Gk1));
+        s = A_(M_(s, dt), tb_gder(smt, eo, k));
+    }
+    *gv = s;
+    *dgv = ds;
+}
+/* g(dx, x, params, t) on the current jets: returns the Bool of the tuple */
+__device__ __forceinline__ bool tb_eval_event(double *__restrict__ smt, const double *par, double t0) {
+#if TB_EV_NOPS > 0
+    tb_ev_k0(smt, par, t0);
+#pragma unroll 1
+    for (int k = 1; k <= TB_P; k++) tb_ev_k(smt, par, t0, k);
+#endif
+    return TB_EV_GATE_EXPR;
+}
+#endif
+
+/* ---- one trajectory ------------------------------------------------------- */
+struct TbTraj {
+    long long i;      /* trajectory index */
+    double t0;        /* current time */
+    double x0[TB_NX]; /* current state */
+    double par[TB_NPAR > 0 ? TB_NPAR : 1];
+    long long nsteps; /* 1-based like the reference */
+    int st;
+    double sign;
+    double tmax;
+#if TB_KIND == 1
+    double g_old, dt, dt_old;
+    bool f_old;
+    int nevents; /* 1-based */
+#endif
+#if TB_KIND == 2
+    double lsum[TB_DOF], lam[TB_DOF], t00;
+#endif
+    /* trange variant */
+    long long iter;
+    double t1;
+};
+
+__device__ __forceinline__ bool tb_isfinite_state(const double *x0) {
+    bool fin = true;
+#pragma unroll
+    for (int c = 0; c < TB_DOF; c++) fin = fin && isfinite(x0[c]);
+    return fin;
+}
+
+/* update_cache!: src/integrator/cache.jl:435-442 */
+__device__ __forceinline__ void tb_update_cache(double *__restrict__ smt, const double *x0) {
+#pragma unroll
+    for (int c = 0; c < TB_NX; c++) S(c, 0) = x0[c];
+}
+
+/* returns true when the trajectory needs no step at all */
+__device__ __forceinline__ bool tb_traj_init(TbTraj &T, double *__restrict__ smt, const TbArgs &a, long long i) {
+    T.i = i;
+    const long long N = a.N;
+#pragma unroll
+    for (int c = 0; c < TB_DOF; c++) T.x0[c] = a.q0[(long long)c * N + i];
+#if TB_KIND == 2
+    /* init_cache_lyap: state = [q; vec(I)]  src/integrator/cache.jl:320-369 */
+#pragma unroll
+    for (int c = 0; c < TB_DOF * TB_DOF; c++) T.x0[TB_DOF + c] = ((c % TB_DOF) == (c / TB_DOF)) ? 1.0 : 0.0;
+#pragma unroll
+    for (int c = 0; c < TB_DOF; c++) { T.lsum[c] = 0.0; T.lam[c] = 0.0; }
+#endif
+#pragma unroll
+    for (int j = 0; j < TB_NPAR; j++) T.par[j] = a.params_per_traj ? a.params[(long long)j * N + i] : a.params[j];
+    T.nsteps = 1;
+    T.st = 0;
+    T.iter = 2;
+    if (a.trange) {
+        T.t0 = a.trange[0];
+        T.t1 = a.trange[1];
+        T.tmax = a.trange[a.nt - 1];
+        /* NaN prefill (src/integrator/cache.jl:313-316) + first column */
+        if (a.xv_trange)
+            for (int c = 0; c < TB_DOF; c++) {
+                a.xv_trange[((long long)c * a.nt) * N + i] = T.x0[c];
+                for (long long j = 1; j < a.nt; j++) a.xv_trange[((long long)c * a.nt + j) * N + i] = TB_NAN;
+            }
+    } else {
+        T.t0 = a.t0;
+        T.tmax = a.tmax;
+        T.t1 = 0.0;
+    }
+    T.sign = copysign(1.0, B_(T.tmax, T.t0));
+    tb_update_cache(smt, T.x0);
+    if (a.tv) a.tv[i] = T.t0;
+    if (a.xv)
+#pragma unroll
+        for (int c = 0; c < TB_DOF; c++) a.xv[((long long)c * a.stride) * N + i] = T.x0[c];
+#if TB_KIND == 2
+    T.t00 = T.t0;
+    if (a.lambda_v)
+#pragma unroll
+        for (int c = 0; c < TB_DOF; c++) a.lambda_v[((long long)c * a.stride) * N + i] = 0.0;
+#endif
+#if TB_KIND == 1
+    /* rootfinding.jl:377-378: g on the initial jets, which the parsed-method
+     * probe (jetcoeffs.jl:181-182 via cache.jl:266) has already filled.       */
+    tb_jetcoeffs(smt, T.par, T.t0);
+    T.f_old = tb_eval_event(smt, T.par, T.t0);
+    T.g_old = TB_EV_G(a.eventorder);
+    T.dt = 0.0;
+    T.dt_old = 0.0;
+    T.nevents = 1;
+#endif
+    return !(M_(T.sign, T.t0) < M_(T.sign, T.tmax));
+}
+
+__device__ __forceinline__ void tb_store_step(const TbTraj &T, const double *__restrict__ smt, const TbArgs &a) {
+    /* called after nsteps += 1: column nsteps-1 */
+    const long long s = T.nsteps - 1, N = a.N;
+    if (s < a.stride) {
+        if (a.tv) a.tv[s * N + T.i] = T.t0;
+        if (a.xv)
+#pragma unroll
+            for (int c = 0; c < TB_DOF; c++) a.xv[((long long)c * a.stride + s) * N + T.i] = T.x0[c];
+    }
+}
+/* set_psol!: src/integrator/taylorinteg.jl:176-186 (polynomial of the step just taken) */
+__device__ __forceinline__ void tb_store_psol(const TbTraj &T, const double *__restrict__ smt, const TbArgs &a) {
+    const long long s = T.nsteps - 1, N = a.N;
+    if (a.psol && s < a.stride)
+        for (int c = 0; c < TB_DOF; c++)
+            for (int k = 0; k <= TB_P; k++) a.psol[(((long long)c * TB_NP1 + k) * a.stride + s) * N + T.i] = S(c, k);
+}
+
+/* One iteration of the driver loop; returns true when the trajectory is done. */
+__device__ __forceinline__ bool tb_traj_step(TbTraj &T, double *__restrict__ smt, const TbArgs &a) {
+#if TB_KIND == 0
+    /* taylorinteg!: src/integrator/taylorinteg.jl:356-378 (t0,tmax) and 607-639 (trange) */
+    tb_jetcoeffs(smt, T.par, T.t0);
+    double dt = tb_stepsize(smt, a);
+    if (dt == 0.0) { T.st |= TB_ST_ZERO_STEP; return true; }
+    const double rem = B_(T.tmax, T.t0);
+    dt = M_(T.sign, fmin(dt, M_(T.sign, rem)));
+#pragma unroll
+    for (int c = 0; c < TB_DOF; c++) T.x0[c] = tb_horner(smt, c, dt);
+    if (a.trange) {
+        const double tnext = A_(T.t0, dt);
+        const long long N = a.N;
+        while (M_(T.sign, T.t1) < M_(T.sign, tnext)) {
+            const double d1 = B_(T.t1, T.t0);
+            if (a.xv_trange)
+                for (int c = 0; c < TB_DOF; c++)
+                    a.xv_trange[((long long)c * a.nt + (T.iter - 1)) * N + T.i] = tb_horner(smt, c, d1);
+            T.iter += 1;
+            T.t1 = a.trange[T.iter - 1];
+        }
+        if (dt == rem) {
+            if (a.xv_trange)
+                for (int c = 0; c < TB_DOF; c++) a.xv_trange[((long long)c * a.nt + (T.iter - 1)) * N + T.i] = T.x0[c];
+            T.t0 = tnext;
+            return true;
+        }
+        T.t0 = tnext;
+        tb_update_cache(smt, T.x0);
+        T.nsteps += 1;
+    } else {
+        tb_store_psol(T, smt, a);
+        T.t0 = A_(T.t0, dt);
+        tb_update_cache(smt, T.x0);
+        T.nsteps += 1;
+        tb_store_step(T, smt, a);
+    }
+    if (T.nsteps > a.maxsteps) { T.st |= TB_ST_MAXSTEPS; return true; }
+    if (!tb_isfinite_state(T.x0)) { T.st |= TB_ST_NONFINITE; return true; }
+    return !(M_(T.sign, T.t0) < M_(T.sign, T.tmax));
+#elif TB_KIND == 1
+    /* taylorinteg!(dense, f!, g, ...): src/rootfinding.jl:392-436; findroot! 176-235 */
+    const int eo = a.eventorder;
+    T.dt_old = T.dt;
+    tb_jetcoeffs(smt, T.par, T.t0);
+    double dt = tb_stepsize(smt, a);
+    dt = M_(T.sign, fmin(dt, M_(T.sign, B_(T.tmax, T.t0))));
+    T.dt = dt;
+#pragma unroll
+    for (int c = 0; c < TB_DOF; c++) T.x0[c] = tb_horner(smt, c, dt);
+    tb_store_psol(T, smt, a);
+    const bool f_now = tb_eval_event(smt, T.par, T.t0);
+    const double g_now = TB_EV_G(eo);
+    if (T.f_old && f_now && (M_(T.g_old, g_now) < 0.0)) { /* surfacecrossing: rootfinding.jl:124-132 */
+        int nriter = 1;
+        const double slope = D_(B_(g_now, T.g_old), T.dt_old);
+        const double dt_li = N_(D_(g_now, slope));
+        double dt_nr = dt_li, gv, dgv;
+        tb_eval_g_dg(smt, eo, dt_nr, &gv, &dgv);
+        while (fabs(gv) > a.nrabstol && nriter <= a.newtoniter) { /* nrconvergencecriterion 147-152 */
+            dt_nr = B_(dt_nr, D_(gv, dgv));
+            tb_eval_g_dg(smt, eo, dt_nr, &gv, &dgv);
+            nriter += 1;
+        }
+        if (nriter == a.newtoniter + 1) T.st |= TB_ST_NR_NOCONV;
+        if (T.nevents <= a.event_cap) {
+            const long long e = T.nevents - 1, N = a.N;
+            if (a.tevents) a.tevents[e * N + T.i] = A_(T.t0, dt_nr);
+            if (a.xevents)
+                for (int c = 0; c < TB_DOF; c++)
+                    a.xevents[((long long)c * a.event_cap + e) * N + T.i] = tb_horner(smt, c, dt_nr);
+            if (a.gresids) a.gresids[e * N + T.i] = gv;
+        } else
+            T.st |= TB_ST_EVENT_OVERFLOW;
+        T.nevents += 1;
+    }
+    T.g_old = g_now;
+    T.f_old = f_now;
+    T.t0 = A_(T.t0, dt);
+    tb_update_cache(smt, T.x0);
+    T.nsteps += 1;
+    tb_store_step(T, smt, a);
+    if (T.nsteps > a.maxsteps) { T.st |= TB_ST_MAXSTEPS; return true; }
+    if (!tb_isfinite_state(T.x0)) { T.st |= TB_ST_NONFINITE; return true; }
+    return !(M_(T.sign, T.t0) < M_(T.sign, T.tmax));
+#else
+    /* lyap_taylorinteg!: src/lyapunovspectrum.jl:379-426; lyap_taylorstep! 226-274 */
+    tb_jetcoeffs(smt, T.par, T.t0);
+#if TB_JAC_NOPS > 0
+    tb_jac_k0(smt, T.par, T.t0);
+#pragma unroll 1
+    for (int k = 1; k < TB_P; k++) tb_jac_k(smt, T.par, T.t0, k);
+#endif
+    /* lyap_jetcoeffs!: lyapunovspectrum.jl:161-211 (generated, unrolled over i3,i2,i1) */
+    tb_var_k0(smt, T.par);
+#pragma unroll 1
+    for (int k = 1; k < TB_P; k++) tb_var_k(smt, T.par, k);
+    double dt = tb_stepsize(smt, a);
+    dt = M_(T.sign, fmin(dt, M_(T.sign, B_(T.tmax, T.t0))));
+#pragma unroll
+    for (int c = 0; c < TB_NX; c++) T.x0[c] = tb_horner(smt, c, dt);
+    double QH[TB_DOF * TB_DOF], Rd[TB_DOF];
+    tb_mgs(&T.x0[TB_DOF], QH, Rd);
+    T.t0 = A_(T.t0, dt);
+    const double tspan = B_(T.t0, T.t00);
+    T.nsteps += 1;
+    {
+        const long long s = T.nsteps - 1, N = a.N;
+        const bool st_ok = s < a.stride;
+        if (a.tv && st_ok) a.tv[s * N + T.i] = T.t0;
+#pragma unroll
+        for (int c = 0; c < TB_DOF; c++) {
+            if (a.xv && st_ok) a.xv[((long long)c * a.stride + s) * N + T.i] = T.x0[c];
+            T.lsum[c] = A_(T.lsum[c], tb_log(Rd[c]));
+            T.lam[c] = D_(T.lsum[c], tspan);
+            if (a.lambda_v && st_ok) a.lambda_v[((long long)c * a.stride + s) * N + T.i] = T.lam[c];
+        }
+    }
+#pragma unroll
+    for (int c = 0; c < TB_DOF * TB_DOF; c++) T.x0[TB_DOF + c] = QH[c];
+    tb_update_cache(smt, T.x0);
+    if (T.nsteps > a.maxsteps) { T.st |= TB_ST_MAXSTEPS; return true; }
+    if (!tb_isfinite_state(T.x0)) { T.st |= TB_ST_NONFINITE; return true; }
+    return !(M_(T.sign, T.t0) < M_(T.sign, T.tmax));
+#endif
+}
+
+__device__ __forceinline__ void tb_traj_finish(const TbTraj &T, const TbArgs &a) {
+    const long long N = a.N, i = T.i;
+    if (a.xfinal)
+#pragma unroll
+        for (int c = 0; c < TB_DOF; c++) a.xfinal[(long long)c * N + i] = T.x0[c];
+    if (a.tfinal) a.tfinal[i] = T.t0;
+    if (a.nsteps) a.nsteps[i] = T.nsteps - 1;
+    if (a.status) a.status[i] = T.st;
+#if TB_KIND == 1
+    if (a.nevents) a.nevents[i] = (T.nevents - 1 < a.event_cap) ? (T.nevents - 1) : a.event_cap;
+#endif
+#if TB_KIND == 2
+    if (a.lambda)
+#pragma unroll
+        for (int c = 0; c < TB_DOF; c++) a.lambda[(long long)c * N + i] = T.lam[c];
+#endif
+}
+
+/* ---- the fused ensemble kernel ---------------------------------------------
+ * Persistent lanes: the grid is sized to the machine (one CTA of TB_BT threads
+ * per SM slot), and every lane pulls trajectory indices from a global queue.
+ * A lane that finishes refills immediately, so lanes of a warp always execute
+ * the same step code whatever their step counts are (no tail of idle lanes);
+ * the loop ends on a warp vote.  With a.lockstep a warp refills only when all
+ * of its lanes are idle and takes 32 consecutive trajectories, which keeps the
+ * per-step stores of tv/xv/psol coalesced.                                    */
+extern "C" __global__ void __launch_bounds__(TB_BT, TB_MINB) tb_ensemble_kernel(const TbArgs a) {
+    extern __shared__ double tb_sm[];
+    double *__restrict__ smt = tb_sm + threadIdx.x;
+    const unsigned full = 0xffffffffu;
+    const int lane = threadIdx.x & 31;
+    TbTraj T;
+    bool have = false;
+    for (;;) {
+        if (a.lockstep) {
+            if (!__any_sync(full, have)) {
+                unsigned long long base = 0;
+                if (lane == 0) base = atomicAdd(a.counter, 32ull);
+                base = __shfl_sync(full, base, 0);
+                if (base >= (unsigned long long)a.N) break;
+                long long i = (long long)base + lane;
+                if (i < a.N) {
+                    have = true;
+                    if (tb_traj_init(T, smt, a, i)) { tb_traj_finish(T, a); have = false; }
+                }
+            }
+        } else {
+            while (!have) {
+                long long i = (long long)atomicAdd(a.counter, 1ull);
+                if (i >= a.N) break;
+                have = true;
+                if (tb_traj_init(T, smt, a, i)) { tb_traj_finish(T, a); have = false; }
+            }
+            if (!__any_sync(full, have)) break;
+        }
+        if (have) {
+            if (tb_traj_step(T, smt, a)) { tb_traj_finish(T, a); have = false; }
+        }
+    }
+}
+
+/* tb_jet: one taylorstep! (src/integrator/taylorstep.jl:59-82) per trajectory;
+ * jets x[dof x (P+1) x N] and the step size.                                   */
+extern "C" __global__ void __launch_bounds__(TB_BT, TB_MINB) tb_jet_kernel(const TbArgs a) {
+    extern __shared__ double tb_sm[];
+    double *__restrict__ smt = tb_sm + threadIdx.x;
+    for (long long i = (long long)blockIdx.x * TB_BT + threadIdx.x; i < a.N; i += (long long)gridDim.x * TB_BT) {
+        double par[TB_NPAR > 0 ? TB_NPAR : 1];
+        for (int j = 0; j < TB_NPAR; j++) par[j] = a.params_per_traj ? a.params[(long long)j * a.N + i] : a.params[j];
+        for (int c = 0; c < TB_DOF; c++) S(c, 0) = a.q0[(long long)c * a.N + i];
+        tb_jetcoeffs(smt, par, a.t0);
+        double dt = tb_stepsize(smt, a);
+        if (a.dtout) a.dtout[i] = dt;
+        if (a.xjet)
+            for (int c = 0; c < TB_DOF; c++)
+                for (int k = 0; k <= TB_P; k++) a.xjet[((long long)c * TB_NP1 + k) * a.N + i] = S(c, k);
+    }
+}
+
+#endif /* TB_DEVICE_DRV_CUH */

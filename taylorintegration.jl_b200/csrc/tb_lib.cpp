@@ -1,0 +1,604 @@
+/*
+ * tb_lib.cpp -- host side of libtaylorb200.so: tape validation, NVRTC
+ * compilation for sm_100a, module loading and launches through the CUDA
+ * driver API (resolved with dlopen so that the library also loads, generates
+ * source and compiles cubins on a machine without a GPU), and the host-buffer
+ * convenience entry points.  See include/taylorb200.h for the contract.
+ *
+ * There is deliberately NO CPU execution path in this library: without a
+ * usable device every tb_integrate* / tb_jet call fails with TB_ERR_CUDA.
+ */
+#include "tb_internal.h"
+
+#include <cuda.h>
+#include <cuda_runtime.h>
+#include <dlfcn.h>
+#include <nvrtc.h>
+
+#include <atomic>
+#include <cmath>
+#include <cstdio>
+#include <cstdlib>
+#include <cstring>
+#include <limits>
+#include <mutex>
+
+namespace tb {
+
+static thread_local std::string g_err;
+void set_error(const std::string &m) { g_err = m; }
+static std::atomic<long long> g_launches{0};
+void count_launch(long long n) { g_launches += n; }
+
+/* ---- driver API, resolved lazily ------------------------------------------ */
+struct Driver {
+    void *h = nullptr;
+    CUresult (*ModuleLoadData)(CUmodule *, const void *) = nullptr;
+    CUresult (*ModuleUnload)(CUmodule) = nullptr;
+    CUresult (*ModuleGetFunction)(CUfunction *, CUmodule, const char *) = nullptr;
+    CUresult (*FuncSetAttribute)(CUfunction, CUfunction_attribute, int) = nullptr;
+    CUresult (*FuncGetAttribute)(int *, CUfunction_attribute, CUfunction) = nullptr;
+    CUresult (*LaunchKernel)(CUfunction, unsigned, unsigned, unsigned, unsigned, unsigned, unsigned, unsigned, CUstream,
+                             void **, void **) = nullptr;
+    CUresult (*GetErrorString)(CUresult, const char **) = nullptr;
+    bool ok = false;
+    std::string why;
+};
+static Driver &driver() {
+    static Driver d;
+    static std::once_flag once;
+    std::call_once(once, [] {
+        d.h = dlopen("libcuda.so.1", RTLD_NOW | RTLD_GLOBAL);
+        if (!d.h) { d.why = "libcuda.so.1 not found: no NVIDIA driver on this machine"; return; }
+#define TB_SYM(field, name)                                                   \
+    *(void **)(&d.field) = dlsym(d.h, name);                                  \
+    if (!d.field) { d.why = std::string("missing driver symbol ") + name; return; }
+        TB_SYM(ModuleLoadData, "cuModuleLoadData")
+        TB_SYM(ModuleUnload, "cuModuleUnload")
+        TB_SYM(ModuleGetFunction, "cuModuleGetFunction")
+        TB_SYM(FuncSetAttribute, "cuFuncSetAttribute")
+        TB_SYM(FuncGetAttribute, "cuFuncGetAttribute")
+        TB_SYM(LaunchKernel, "cuLaunchKernel")
+        TB_SYM(GetErrorString, "cuGetErrorString")
+#undef TB_SYM
+        d.ok = true;
+    });
+    return d;
+}
+static std::string cu_err(CUresult r) {
+    const char *s = nullptr;
+    if (driver().ok) driver().GetErrorString(r, &s);
+    return s ? s : ("CUresult " + std::to_string((int)r));
+}
+#define TB_CUDA(call)                                                                                   \
+    do {                                                                                                \
+        cudaError_t e_ = (call);                                                                        \
+        if (e_ != cudaSuccess) {                                                                        \
+            set_error(std::string(#call) + ": " + cudaGetErrorString(e_));                              \
+            return TB_ERR_CUDA;                                                                         \
+        }                                                                                               \
+    } while (0)
+
+/* mirrors struct TbArgs of tb_device_pre.cuh */
+struct TbArgs {
+    long long N;
+    const double *q0;
+    const double *params;
+    const double *trange;
+    long long nt;
+    double t0, tmax;
+    double abstol, reltol, minstep, maxstep, nrabstol;
+    long long maxsteps;
+    long long stride;
+    int params_per_traj;
+    int eventorder, newtoniter, event_cap;
+    int lockstep;
+    int pad0;
+    double *xfinal;
+    double *tfinal;
+    long long *nsteps;
+    int *status;
+    double *xv_trange;
+    double *tv;
+    double *xv;
+    double *psol;
+    double *tevents;
+    double *xevents;
+    double *gresids;
+    int *nevents;
+    double *lambda;
+    double *lambda_v;
+    unsigned long long *counter;
+    double *xjet;
+    double *dtout;
+};
+static_assert(sizeof(TbArgs) == 272, "TbArgs layout must match tb_device_pre.cuh");
+
+struct Loaded {
+    CUmodule mod = nullptr;
+    CUfunction ensemble = nullptr, jet = nullptr;
+    int sm_count = 0;
+};
+
+} // namespace tb
+
+struct tb_ode {
+    tb::Ode o;
+};
+
+struct tb_kernel {
+    tb::Ode ode;
+    tb_compile_opts_t co;
+    tb::Layout L;
+    std::string source, log;
+    std::vector<char> cubin;
+    int regs = -1, local_bytes = -1;
+    std::mutex mu;
+    std::map<int, tb::Loaded> loaded; /* per device */
+    /* grow-only device arena for the host-buffer entry points, per device */
+    std::map<int, std::pair<char *, size_t>> arena;
+};
+
+namespace tb {
+
+static int arity_ok(const tb_op_t &op, std::string &why) {
+    auto kind = [](int32_t o) { return TB_OPERAND_KIND(o); };
+    auto series = [&](int32_t o) { int k = kind(o); return k == TB_K_X || k == TB_K_DX || k == TB_K_TMP || k == TB_K_TIME; };
+    auto number = [&](int32_t o) { int k = kind(o); return k == TB_K_PAR || k == TB_K_IMM; };
+    if (kind(op.res) != TB_K_DX && kind(op.res) != TB_K_TMP) { why = "result must be a dx or tmp series"; return 0; }
+    switch (op.op) {
+        case TB_OP_IDENTITY: if (!series(op.a) && !number(op.a)) { why = "identity! needs an argument"; return 0; } break;
+        case TB_OP_ZERO: case TB_OP_ONE: break;
+        case TB_OP_NEG: case TB_OP_SQR: case TB_OP_SQRT: case TB_OP_EXP: case TB_OP_LOG: case TB_OP_POW:
+            /* pow!/sqr!/... need a series base: a plain number makes the generated
+             * method throw in the reference too (test/taylorize.jl:953-992)       */
+            if (!series(op.a)) { why = "unary Taylor primitive needs a series argument"; return 0; }
+            break;
+        case TB_OP_SINCOS:
+            if (!series(op.a)) { why = "sincos! needs a series argument"; return 0; }
+            if (kind(op.aux) != TB_K_TMP && kind(op.aux) != TB_K_DX) { why = "sincos! needs an auxiliary series"; return 0; }
+            break;
+        case TB_OP_ADD: case TB_OP_SUB: case TB_OP_MUL: case TB_OP_DIV:
+            if (!(series(op.a) || number(op.a)) || !(series(op.b) || number(op.b))) { why = "binary op needs two arguments"; return 0; }
+            break;
+        default: why = "opcode " + std::to_string(op.op) + " is not implemented"; return 0;
+    }
+    return 1;
+}
+
+static int validate(const tb_ode_desc_t &d, std::string &why) {
+    if (d.dof < 1 || d.dof > 4096) { why = "dof out of range"; return 0; }
+    if (d.npar < 0 || d.ntmp < 0 || d.nops < 1 || d.ev_nops < 0 || d.jac_nops < 0) { why = "negative count"; return 0; }
+    if (!d.ops) { why = "ops is NULL"; return 0; }
+    const int total = d.nops + d.ev_nops + d.jac_nops;
+    for (int j = 0; j < total; j++) {
+        const tb_op_t &op = d.ops[j];
+        std::string w;
+        if (!arity_ok(op, w)) { why = "op " + std::to_string(j) + ": " + w; return 0; }
+        const int32_t all[4] = {op.res, op.a, op.b, op.aux};
+        for (int32_t o : all) {
+            int k = TB_OPERAND_KIND(o), i = TB_OPERAND_INDEX(o);
+            bool ok = true;
+            switch (k) {
+                case TB_K_NONE: case TB_K_IMM: case TB_K_TIME: break;
+                case TB_K_X: case TB_K_DX: ok = i < d.dof; break;
+                case TB_K_TMP: ok = i < d.ntmp; break;
+                case TB_K_PAR: ok = i < d.npar; break;
+                default: ok = false;
+            }
+            if (!ok) { why = "op " + std::to_string(j) + ": operand out of range"; return 0; }
+        }
+    }
+    if (d.has_jac && !d.jac) { why = "has_jac set but jac is NULL"; return 0; }
+    return 1;
+}
+
+/* parse "Used N registers" / "bytes stack frame" of the ptxas -v log for the ensemble kernel */
+static void parse_ptxas(const std::string &log, int *regs, int *local_bytes) {
+    size_t p = log.find("tb_ensemble_kernel");
+    if (p == std::string::npos) return;
+    size_t q = log.find("Used ", p);
+    if (q != std::string::npos) *regs = atoi(log.c_str() + q + 5);
+    size_t s = log.find("bytes stack frame", p);
+    if (s != std::string::npos) {
+        size_t b = log.rfind('\n', s);
+        *local_bytes = atoi(log.c_str() + (b == std::string::npos ? 0 : b + 1));
+    }
+}
+
+static int get_device(int *dev) {
+    int n = 0;
+    cudaError_t e = cudaGetDeviceCount(&n);
+    if (e != cudaSuccess || n == 0) {
+        set_error(std::string("no usable CUDA device: ") + (e != cudaSuccess ? cudaGetErrorString(e) : "device count is 0"));
+        return TB_ERR_CUDA;
+    }
+    TB_CUDA(cudaGetDevice(dev));
+    return TB_OK;
+}
+
+static int ensure_loaded(tb_kernel *k, Loaded **out) {
+    int dev = 0;
+    int rc = get_device(&dev);
+    if (rc) return rc;
+    std::lock_guard<std::mutex> lk(k->mu);
+    auto it = k->loaded.find(dev);
+    if (it != k->loaded.end()) { *out = &it->second; return TB_OK; }
+    Driver &d = driver();
+    if (!d.ok) { set_error(d.why); return TB_ERR_CUDA; }
+    TB_CUDA(cudaFree(0)); /* make the primary context current */
+    Loaded l;
+    CUresult r = d.ModuleLoadData(&l.mod, k->cubin.data());
+    if (r != CUDA_SUCCESS) { set_error("cuModuleLoadData: " + cu_err(r)); return TB_ERR_CUDA; }
+    r = d.ModuleGetFunction(&l.ensemble, l.mod, "tb_ensemble_kernel");
+    if (r != CUDA_SUCCESS) { set_error("cuModuleGetFunction(tb_ensemble_kernel): " + cu_err(r)); return TB_ERR_CUDA; }
+    r = d.ModuleGetFunction(&l.jet, l.mod, "tb_jet_kernel");
+    if (r != CUDA_SUCCESS) { set_error("cuModuleGetFunction(tb_jet_kernel): " + cu_err(r)); return TB_ERR_CUDA; }
+    for (CUfunction f : {l.ensemble, l.jet}) {
+        r = d.FuncSetAttribute(f, CU_FUNC_ATTRIBUTE_MAX_DYNAMIC_SHARED_SIZE_BYTES, (int)k->L.smem_bytes);
+        if (r != CUDA_SUCCESS) { set_error("cuFuncSetAttribute(max dynamic smem): " + cu_err(r)); return TB_ERR_CUDA; }
+    }
+    int v = 0;
+    if (d.FuncGetAttribute(&v, CU_FUNC_ATTRIBUTE_NUM_REGS, l.ensemble) == CUDA_SUCCESS) k->regs = v;
+    if (d.FuncGetAttribute(&v, CU_FUNC_ATTRIBUTE_LOCAL_SIZE_BYTES, l.ensemble) == CUDA_SUCCESS) k->local_bytes = v;
+    cudaDeviceProp prop;
+    TB_CUDA(cudaGetDeviceProperties(&prop, dev));
+    l.sm_count = prop.multiProcessorCount;
+    k->loaded[dev] = l;
+    *out = &k->loaded[dev];
+    return TB_OK;
+}
+
+static void fill_args(TbArgs &a, int64_t N, const double *q0, const double *params, double t0, double tmax,
+                      const double *trange, int64_t nt, const tb_opts_t &o, const tb_out_t &out, void *work) {
+    memset(&a, 0, sizeof a);
+    a.N = N;
+    a.q0 = q0;
+    a.params = params;
+    a.trange = trange;
+    a.nt = nt;
+    a.t0 = t0;
+    a.tmax = tmax;
+    a.abstol = o.abstol;
+    a.reltol = o.reltol;
+    a.minstep = o.minstepsize;
+    a.maxstep = o.maxstepsize;
+    a.nrabstol = o.nrabstol;
+    a.maxsteps = o.maxsteps;
+    a.stride = o.steps_stride ? o.steps_stride : o.maxsteps + 1;
+    a.params_per_traj = o.params_per_traj;
+    a.eventorder = o.eventorder;
+    a.newtoniter = o.newtoniter;
+    a.event_cap = o.event_capacity > 0 ? o.event_capacity : (int)(o.maxsteps + 1);
+    a.lockstep = (out.tv || out.xv || out.psol || out.lambda_v) ? 1 : 0;
+    a.xfinal = out.xfinal;
+    a.tfinal = out.tfinal;
+    a.nsteps = (long long *)out.nsteps;
+    a.status = out.status;
+    a.xv_trange = out.xv_trange;
+    a.tv = out.tv;
+    a.xv = out.xv;
+    a.psol = out.psol;
+    a.tevents = out.tevents;
+    a.xevents = out.xevents;
+    a.gresids = out.gresids;
+    a.nevents = out.nevents;
+    a.lambda = out.lambda;
+    a.lambda_v = out.lambda_v;
+    a.counter = (unsigned long long *)work;
+}
+
+static int launch(tb_kernel *k, Loaded *l, CUfunction f, TbArgs &a, bool persistent, cudaStream_t stream) {
+    Driver &d = driver();
+    const int bt = k->L.block_threads;
+    long long want = (a.N + bt - 1) / bt;
+    long long cap = (long long)l->sm_count * k->L.blocks_per_sm;
+    unsigned grid = (unsigned)std::max<long long>(1, persistent ? std::min(want, cap) : std::min<long long>(want, cap * 4));
+    void *params[1] = {&a};
+    CUresult r = d.LaunchKernel(f, grid, 1, 1, (unsigned)bt, 1, 1, (unsigned)k->L.smem_bytes, (CUstream)stream, params, nullptr);
+    if (r != CUDA_SUCCESS) { set_error("cuLaunchKernel: " + cu_err(r)); return TB_ERR_CUDA; }
+    count_launch(1);
+    return TB_OK;
+}
+
+/* bump allocator over the kernel's per-device arena */
+struct Arena {
+    char *base = nullptr;
+    size_t cap = 0, off = 0;
+    template <class T> T *take(size_t n) {
+        size_t bytes = (n * sizeof(T) + 255) & ~(size_t)255;
+        T *p = (T *)(base + off);
+        off += bytes;
+        return off <= cap ? p : nullptr;
+    }
+};
+static size_t rup(size_t b) { return (b + 255) & ~(size_t)255; }
+
+static int arena_get(tb_kernel *k, size_t bytes, Arena &A) {
+    int dev = 0;
+    int rc = get_device(&dev);
+    if (rc) return rc;
+    std::lock_guard<std::mutex> lk(k->mu);
+    auto &slot = k->arena[dev];
+    if (slot.second < bytes) {
+        if (slot.first) cudaFree(slot.first);
+        slot = {nullptr, 0};
+        char *p = nullptr;
+        TB_CUDA(cudaMalloc(&p, bytes));
+        slot = {p, bytes};
+    }
+    A.base = slot.first;
+    A.cap = slot.second;
+    A.off = 0;
+    return TB_OK;
+}
+
+static int integrate_host(tb_kernel *k, int64_t N, const double *q0, const double *params, double t0, double tmax,
+                          const double *trange, int64_t nt, const tb_opts_t *opts, tb_out_t *out) {
+    if (!k || !opts || !out || N < 0 || !q0) { set_error("tb_integrate: bad argument"); return TB_ERR_ARG; }
+    if (trange && nt < 2) { set_error("tb_integrate_trange: trange needs at least two points"); return TB_ERR_ARG; }
+    if (trange && k->co.kind != TB_KIND_PLAIN) { set_error("trange is implemented for TB_KIND_PLAIN kernels"); return TB_ERR_UNSUPPORTED; }
+    const tb_ode_desc_t &d = k->ode.desc;
+    if (d.npar > 0 && !params) { set_error("tb_integrate: params is NULL"); return TB_ERR_ARG; }
+    if (k->co.kind == TB_KIND_EVENTS && opts->eventorder > k->co.order) { set_error("order must be >= eventorder (rootfinding.jl:321)"); return TB_ERR_ARG; }
+    if (N == 0) return TB_OK;
+    Loaded *l = nullptr;
+    int rc = ensure_loaded(k, &l);
+    if (rc) return rc;
+    const size_t dof = d.dof, n = (size_t)N, np1 = k->co.order + 1;
+    const size_t stride = opts->steps_stride ? opts->steps_stride : opts->maxsteps + 1;
+    const size_t cap = opts->event_capacity > 0 ? opts->event_capacity : (size_t)(opts->maxsteps + 1);
+    const size_t npar_elems = d.npar ? (opts->params_per_traj ? (size_t)d.npar * n : (size_t)d.npar) : 0;
+    struct Item { void **dptr; void *host; size_t bytes; };
+    tb_out_t dv;
+    memset(&dv, 0, sizeof dv);
+    std::vector<Item> outs;
+    auto want = [&](void *host, void **dptr, size_t bytes) { if (host) outs.push_back({dptr, host, bytes}); };
+    want(out->xfinal, (void **)&dv.xfinal, dof * n * 8);
+    want(out->tfinal, (void **)&dv.tfinal, n * 8);
+    want(out->nsteps, (void **)&dv.nsteps, n * 8);
+    want(out->status, (void **)&dv.status, n * 4);
+    if (trange) want(out->xv_trange, (void **)&dv.xv_trange, dof * (size_t)nt * n * 8);
+    else {
+        want(out->tv, (void **)&dv.tv, stride * n * 8);
+        want(out->xv, (void **)&dv.xv, dof * stride * n * 8);
+        want(out->psol, (void **)&dv.psol, dof * np1 * stride * n * 8);
+    }
+    if (k->co.kind == TB_KIND_EVENTS) {
+        want(out->tevents, (void **)&dv.tevents, cap * n * 8);
+        want(out->xevents, (void **)&dv.xevents, dof * cap * n * 8);
+        want(out->gresids, (void **)&dv.gresids, cap * n * 8);
+        want(out->nevents, (void **)&dv.nevents, n * 4);
+    }
+    if (k->co.kind == TB_KIND_LYAP) {
+        want(out->lambda, (void **)&dv.lambda, dof * n * 8);
+        if (!trange) want(out->lambda_v, (void **)&dv.lambda_v, dof * stride * n * 8);
+    }
+    size_t total = rup(256) + rup(dof * n * 8) + rup(npar_elems * 8) + rup((size_t)(trange ? nt : 0) * 8);
+    for (auto &it : outs) total += rup(it.bytes);
+    Arena A;
+    rc = arena_get(k, total, A);
+    if (rc) return rc;
+    cudaStream_t st = 0;
+    void *work = A.take<char>(256);
+    double *d_q0 = A.take<double>(dof * n);
+    double *d_par = npar_elems ? A.take<double>(npar_elems) : nullptr;
+    double *d_tr = trange ? A.take<double>((size_t)nt) : nullptr;
+    for (auto &it : outs) *it.dptr = A.take<char>(it.bytes);
+    TB_CUDA(cudaMemsetAsync(work, 0, 256, st));
+    TB_CUDA(cudaMemcpyAsync(d_q0, q0, dof * n * 8, cudaMemcpyHostToDevice, st));
+    if (d_par) TB_CUDA(cudaMemcpyAsync(d_par, params, npar_elems * 8, cudaMemcpyHostToDevice, st));
+    if (d_tr) TB_CUDA(cudaMemcpyAsync(d_tr, trange, (size_t)nt * 8, cudaMemcpyHostToDevice, st));
+    /* buffers the kernel fills only partially start from zero */
+    for (auto &it : outs)
+        if (it.host == out->tv || it.host == out->xv || it.host == out->psol || it.host == out->tevents ||
+            it.host == out->xevents || it.host == out->gresids || it.host == out->lambda_v)
+            TB_CUDA(cudaMemsetAsync(*it.dptr, 0, it.bytes, st));
+    TbArgs a;
+    fill_args(a, N, d_q0, d_par, t0, tmax, d_tr, nt, *opts, dv, work);
+    rc = launch(k, l, l->ensemble, a, true, st);
+    if (rc) return rc;
+    for (auto &it : outs) TB_CUDA(cudaMemcpyAsync(it.host, *it.dptr, it.bytes, cudaMemcpyDeviceToHost, st));
+    TB_CUDA(cudaStreamSynchronize(st));
+    return TB_OK;
+}
+
+} // namespace tb
+
+using namespace tb;
+
+extern "C" {
+
+int tb_abi_version(void) { return TB_ABI_VERSION; }
+const char *tb_last_error(void) { return g_err.c_str(); }
+
+tb_ode_t *tb_ode_create(const tb_ode_desc_t *desc) {
+    if (!desc) { set_error("tb_ode_create: NULL description"); return nullptr; }
+    std::string why;
+    if (!validate(*desc, why)) { set_error("tb_ode_create: " + why); return nullptr; }
+    tb_ode_t *o = new tb_ode_t;
+    o->o.desc = *desc;
+    const int total = desc->nops + desc->ev_nops + desc->jac_nops;
+    o->o.ops.assign(desc->ops, desc->ops + total);
+    if (desc->has_jac) o->o.jac.assign(desc->jac, desc->jac + (size_t)desc->dof * desc->dof);
+    o->o.desc.ops = o->o.ops.data();
+    o->o.desc.jac = desc->has_jac ? o->o.jac.data() : nullptr;
+    return o;
+}
+void tb_ode_free(tb_ode_t *ode) { delete ode; }
+
+void tb_opts_default(tb_opts_t *o) {
+    if (!o) return;
+    memset(o, 0, sizeof *o);
+    o->abstol = 1e-20;
+    o->reltol = 0.0;
+    o->minstepsize = 0.0;
+    o->maxstepsize = std::numeric_limits<double>::infinity();
+    o->maxsteps = 500;
+    o->eventorder = 0;
+    o->newtoniter = 10;
+    o->nrabstol = std::numeric_limits<double>::epsilon();
+    o->event_capacity = 0;
+    o->params_per_traj = 0;
+    o->steps_stride = 0;
+}
+void tb_compile_opts_default(tb_compile_opts_t *o) {
+    if (!o) return;
+    memset(o, 0, sizeof *o);
+    o->order = 28;
+    o->mode = TB_MODE_PARITY;
+    o->kind = TB_KIND_PLAIN;
+}
+
+const char *tb_generate_source(const tb_ode_t *ode, const tb_compile_opts_t *co) {
+    static thread_local std::string src;
+    if (!ode || !co) { set_error("tb_generate_source: NULL argument"); return nullptr; }
+    Layout L;
+    std::string err;
+    if (generate(ode->o, *co, L, src, err) != TB_OK) { set_error("tb_generate_source: " + err); return nullptr; }
+    return src.c_str();
+}
+
+tb_kernel_t *tb_compile(const tb_ode_t *ode, const tb_compile_opts_t *co) {
+    if (!ode || !co) { set_error("tb_compile: NULL argument"); return nullptr; }
+    tb_kernel_t *k = new tb_kernel_t;
+    k->ode = ode->o;
+    k->ode.desc.ops = k->ode.ops.data();
+    k->ode.desc.jac = k->ode.desc.has_jac ? k->ode.jac.data() : nullptr;
+    k->co = *co;
+    std::string err;
+    if (generate(k->ode, k->co, k->L, k->source, err) != TB_OK) {
+        set_error("tb_compile: " + err);
+        delete k;
+        return nullptr;
+    }
+    nvrtcProgram prog;
+    if (nvrtcCreateProgram(&prog, k->source.c_str(), "tb_kernel.cu", 0, nullptr, nullptr) != NVRTC_SUCCESS) {
+        set_error("nvrtcCreateProgram failed");
+        delete k;
+        return nullptr;
+    }
+    std::vector<const char *> o = {"--gpu-architecture=sm_100a", "-std=c++17", "-lineinfo", "--ptxas-options=-v",
+                                   "-default-device"};
+    o.push_back(k->co.mode == TB_MODE_PARITY ? "--fmad=false" : "--fmad=true");
+    o.push_back("--prec-div=true");
+    o.push_back("--prec-sqrt=true");
+    nvrtcResult r = nvrtcCompileProgram(prog, (int)o.size(), o.data());
+    size_t ls = 0;
+    nvrtcGetProgramLogSize(prog, &ls);
+    k->log.resize(ls);
+    if (ls) nvrtcGetProgramLog(prog, &k->log[0]);
+    if (r != NVRTC_SUCCESS) {
+        set_error(std::string("NVRTC: ") + nvrtcGetErrorString(r) + "\n" + k->log);
+        nvrtcDestroyProgram(&prog);
+        delete k;
+        return nullptr;
+    }
+    size_t cs = 0;
+    nvrtcGetCUBINSize(prog, &cs);
+    k->cubin.resize(cs);
+    nvrtcGetCUBIN(prog, k->cubin.data());
+    nvrtcDestroyProgram(&prog);
+    parse_ptxas(k->log, &k->regs, &k->local_bytes);
+    return k;
+}
+
+void tb_kernel_free(tb_kernel_t *k) {
+    if (!k) return;
+    for (auto &kv : k->loaded)
+        if (kv.second.mod && driver().ok) driver().ModuleUnload(kv.second.mod);
+    for (auto &kv : k->arena)
+        if (kv.second.first) cudaFree(kv.second.first);
+    delete k;
+}
+const char *tb_kernel_source(const tb_kernel_t *k) { return k ? k->source.c_str() : nullptr; }
+const char *tb_kernel_log(const tb_kernel_t *k) { return k ? k->log.c_str() : nullptr; }
+int tb_kernel_info(const tb_kernel_t *k, int *regs, int *smem_bytes, int *local_bytes, int *block_threads, int *blocks_per_sm) {
+    if (!k) return TB_ERR_ARG;
+    if (regs) *regs = k->regs;
+    if (smem_bytes) *smem_bytes = (int)k->L.smem_bytes;
+    if (local_bytes) *local_bytes = k->local_bytes;
+    if (block_threads) *block_threads = k->L.block_threads;
+    if (blocks_per_sm) *blocks_per_sm = k->L.blocks_per_sm;
+    return TB_OK;
+}
+const void *tb_kernel_cubin(const tb_kernel_t *k, size_t *nbytes) {
+    if (!k) return nullptr;
+    if (nbytes) *nbytes = k->cubin.size();
+    return k->cubin.data();
+}
+
+int tb_integrate(tb_kernel_t *k, int64_t N, const double *q0, const double *params, double t0, double tmax,
+                 const tb_opts_t *opts, tb_out_t *out) {
+    return integrate_host(k, N, q0, params, t0, tmax, nullptr, 0, opts, out);
+}
+int tb_integrate_trange(tb_kernel_t *k, int64_t N, const double *q0, const double *params, const double *trange,
+                        int64_t nt, const tb_opts_t *opts, tb_out_t *out) {
+    if (!trange) { set_error("tb_integrate_trange: trange is NULL"); return TB_ERR_ARG; }
+    return integrate_host(k, N, q0, params, trange[0], trange[nt > 0 ? nt - 1 : 0], trange, nt, opts, out);
+}
+
+size_t tb_work_bytes(void) { return 256; }
+
+int tb_integrate_device(tb_kernel_t *k, int64_t N, const double *d_q0, const double *d_params, double t0, double tmax,
+                        const double *d_trange, int64_t nt, const tb_opts_t *opts, const tb_out_t *d_out, void *d_work,
+                        void *stream) {
+    if (!k || !opts || !d_out || !d_work || N < 0) { set_error("tb_integrate_device: bad argument"); return TB_ERR_ARG; }
+    if (d_trange && k->co.kind != TB_KIND_PLAIN) { set_error("trange is implemented for TB_KIND_PLAIN kernels"); return TB_ERR_UNSUPPORTED; }
+    if (N == 0) return TB_OK;
+    Loaded *l = nullptr;
+    int rc = ensure_loaded(k, &l);
+    if (rc) return rc;
+    cudaStream_t st = (cudaStream_t)stream;
+    TB_CUDA(cudaMemsetAsync(d_work, 0, 8, st));
+    TbArgs a;
+    fill_args(a, N, d_q0, d_params, t0, tmax, d_trange, nt, *opts, *d_out, d_work);
+    return launch(k, l, l->ensemble, a, true, st);
+}
+
+int64_t tb_launch_count(void) { return g_launches.load(); }
+
+int tb_jet(tb_kernel_t *k, int64_t N, const double *q0, const double *params, double t0, const tb_opts_t *opts,
+           double *xjet, double *dt) {
+    if (!k || !opts || !q0 || N < 0) { set_error("tb_jet: bad argument"); return TB_ERR_ARG; }
+    if (N == 0) return TB_OK;
+    Loaded *l = nullptr;
+    int rc = ensure_loaded(k, &l);
+    if (rc) return rc;
+    const tb_ode_desc_t &d = k->ode.desc;
+    const size_t dof = d.dof, n = (size_t)N, np1 = k->co.order + 1;
+    const size_t npar_elems = d.npar ? (opts->params_per_traj ? (size_t)d.npar * n : (size_t)d.npar) : 0;
+    Arena A;
+    rc = arena_get(k, rup(dof * n * 8) + rup(npar_elems * 8) + rup(dof * np1 * n * 8) + rup(n * 8) + 256, A);
+    if (rc) return rc;
+    double *d_q0 = A.take<double>(dof * n);
+    double *d_par = npar_elems ? A.take<double>(npar_elems) : nullptr;
+    double *d_jet = A.take<double>(dof * np1 * n);
+    double *d_dt = A.take<double>(n);
+    TB_CUDA(cudaMemcpy(d_q0, q0, dof * n * 8, cudaMemcpyHostToDevice));
+    if (d_par) TB_CUDA(cudaMemcpy(d_par, params, npar_elems * 8, cudaMemcpyHostToDevice));
+    TbArgs a;
+    tb_out_t none;
+    memset(&none, 0, sizeof none);
+    fill_args(a, N, d_q0, d_par, t0, t0, nullptr, 0, *opts, none, nullptr);
+    a.xjet = d_jet;
+    a.dtout = d_dt;
+    rc = launch(k, l, l->jet, a, false, 0);
+    if (rc) return rc;
+    TB_CUDA(cudaDeviceSynchronize());
+    if (xjet) TB_CUDA(cudaMemcpy(xjet, d_jet, dof * np1 * n * 8, cudaMemcpyDeviceToHost));
+    if (dt) TB_CUDA(cudaMemcpy(dt, d_dt, n * 8, cudaMemcpyDeviceToHost));
+    return TB_OK;
+}
+
+int tb_device_count(void) {
+    int n = 0;
+    if (cudaGetDeviceCount(&n) != cudaSuccess) return 0;
+    return n;
+}
+int tb_set_device(int device) {
+    TB_CUDA(cudaSetDevice(device));
+    return TB_OK;
+}
+
+} /* extern "C" */
