@@ -233,15 +233,15 @@ TB_HD double tb_pow(double x, double y) {
  * carried as a pair (r, rl).                                                  */
 TB_HD double tb_ksin(double x, double y) { /* sin(x + y), |x| <= pi/4 */
     double z = TB_MUL(x, x);
-    double p = -1.0 / 51090942171709440000.0;        /* -1/21! */
-    p = TB_FMA(p, z, 1.0 / 121645100408832000.0);    /*  1/19! */
-    p = TB_FMA(p, z, -1.0 / 355687428096000.0);      /* -1/17! */
-    p = TB_FMA(p, z, 1.0 / 1307674368000.0);         /*  1/15! */
-    p = TB_FMA(p, z, -1.0 / 6227020800.0);           /* -1/13! */
-    p = TB_FMA(p, z, 1.0 / 39916800.0);              /*  1/11! */
-    p = TB_FMA(p, z, -1.0 / 362880.0);               /* -1/9!  */
-    p = TB_FMA(p, z, 1.0 / 5040.0);                  /*  1/7!  */
-    p = TB_FMA(p, z, -1.0 / 120.0);                  /* -1/5!  */
+    double p = 1.0 / 51090942171709440000.0;         /*  1/21! */
+    p = TB_FMA(p, z, -1.0 / 121645100408832000.0);   /* -1/19! */
+    p = TB_FMA(p, z, 1.0 / 355687428096000.0);       /*  1/17! */
+    p = TB_FMA(p, z, -1.0 / 1307674368000.0);        /* -1/15! */
+    p = TB_FMA(p, z, 1.0 / 6227020800.0);            /*  1/13! */
+    p = TB_FMA(p, z, -1.0 / 39916800.0);             /* -1/11! */
+    p = TB_FMA(p, z, 1.0 / 362880.0);                /*  1/9!  */
+    p = TB_FMA(p, z, -1.0 / 5040.0);                 /* -1/7!  */
+    p = TB_FMA(p, z, 1.0 / 120.0);                   /*  1/5!  */
     /* sin = x + (x*z*(-1/6 + z*p) + y*(1 - z/2)) */
     double v = TB_MUL(z, x);
     double w = TB_FMA(z, p, -1.0 / 6.0);
