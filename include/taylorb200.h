@@ -174,13 +174,14 @@ typedef struct tb_compile_opts {
     int32_t mode;          /* tb_mode                                         */
     int32_t kind;          /* tb_kind                                         */
     int32_t block_threads; /* 0 = default                                     */
-    int32_t reg_budget;    /* fast mode: doubles of jet storage kept in registers per trajectory (0 = default) */
+    int32_t reg_budget;    /* variant 2: doubles of jet storage kept in registers per trajectory (0 = default: 3 series, <0 = none) */
     int32_t min_blocks_per_sm; /* 0 = default                                 */
     int32_t flags;         /* TB_CF_*                                         */
     int32_t reserved;
 } tb_compile_opts_t;
 #define TB_CF_NO_DISK_CACHE 1 /* do not read/write the on-disk cubin cache    */
 #define TB_CF_KEEP_SOURCE 2   /* (always on) keep generated source for tb_get_source */
+#define TB_CF_ROLLED 4        /* force kernel variant 1 (rolled loops, all jets in shared memory) */
 
 /* ---- integration options: keyword arguments of taylorinteg -------------- */
 typedef struct tb_opts {

@@ -353,6 +353,7 @@ int generate(const Ode &ode, const tb_compile_opts_t &co, Layout &L, std::string
     if (co.kind == TB_KIND_LYAP && !d.has_jac) { err = "TB_KIND_LYAP needs a Jacobian description"; return TB_ERR_ARG; }
     if (co.kind == TB_KIND_EVENTS && TB_OPERAND_KIND(d.ev_g) == TB_K_NONE) { err = "TB_KIND_EVENTS needs an event function"; return TB_ERR_ARG; }
     Gen g(ode, co, L);
+    L.variant = 1;
     g.analyse();
     /* block size: as many trajectories per SM as shared memory holds */
     const size_t per_traj = (size_t)L.nslot * (co.order + 1) * sizeof(double);
@@ -375,6 +376,7 @@ int generate(const Ode &ode, const tb_compile_opts_t &co, Layout &L, std::string
 
     Emitter e;
     e.line("/* generated by libtaylorb200 tb_codegen.cpp -- do not edit */");
+    e.line("#define TB_VARIANT 1");
     e.line("#define TB_P %d", co.order);
     e.line("#define TB_DOF %d", d.dof);
     e.line("#define TB_NX %d", L.nx);
@@ -412,6 +414,17 @@ int generate(const Ode &ode, const tb_compile_opts_t &co, Layout &L, std::string
     if (!g.err.empty()) { err = g.err; return TB_ERR_ARG; }
     src.swap(e.s);
     return TB_OK;
+}
+
+int generate_any(const Ode &ode, const tb_compile_opts_t &co, Layout &L, std::string &src, std::string &err) {
+    if (!(co.flags & TB_CF_ROLLED)) {
+        std::string e2;
+        Layout L2;
+        int rc = generate_unrolled(ode, co, L2, src, e2);
+        if (rc == TB_OK) { L = L2; return rc; }
+        if (rc != TB_ERR_UNSUPPORTED) { err = e2; return rc; }
+    }
+    return generate(ode, co, L, src, err);
 }
 
 } // namespace tb

@@ -13,19 +13,25 @@
 #ifndef TB_DEVICE_DRV_CUH
 #define TB_DEVICE_DRV_CUH
 
+#ifndef TB_VARIANT
+#define TB_VARIANT 1
+#endif
+
+/* _stepsize: src/integrator/stepsize.jl:107-111   (eps/a)^(1/k).  Not inlined: the
+ * double-double pow is ~300 instructions and is called 2*dof times per step.    */
+__device__ __noinline__ double tb_stepsize_k(double a, double eps, int k) {
+    double aux = D_(eps, a);
+    double kinv = D_(1.0, (double)k);
+    return tb_pow(aux, kinv);
+}
+
+#if TB_VARIANT == 1
 /* evaluate(a::Taylor1, dt): Horner, s = a[P]; s = s*dt + a[k]  (TaylorSeries) */
 __device__ __forceinline__ double tb_horner(const double *__restrict__ smt, int slot, double dt) {
     double s = S(slot, TB_P);
 #pragma unroll 4
     for (int k = TB_P - 1; k >= 0; k--) s = A_(M_(s, dt), S(slot, k));
     return s;
-}
-
-/* _stepsize: src/integrator/stepsize.jl:107-111   (eps/a)^(1/k) */
-__device__ __forceinline__ double tb_stepsize_k(double a, double eps, int k) {
-    double aux = D_(eps, a);
-    double kinv = D_(1.0, (double)k);
-    return tb_pow(aux, kinv);
 }
 
 /* stepsize(x::Taylor1, abs, rel): stepsize.jl:58-77 */
@@ -81,6 +87,88 @@ __device__ __forceinline__ void tb_jetcoeffs(double *__restrict__ smt, const dou
 #pragma unroll 1
     for (int k = 1; k < TB_P; k++) tb_rhs_k(smt, par, t0, k);
 }
+
+#endif /* TB_VARIANT == 1 */
+
+#if TB_VARIANT == 2
+/* ---- variant 2: jets in registers / shared memory / derived, static indices ----
+ * TB_X(c, k) is coefficient k of state jet c; every loop over (c, k) below has
+ * constant bounds and is fully unrolled, so each access resolves at compile time
+ * to a register, one LDS, or a scaled dx coefficient.                            */
+#define TB_X(c, k) tb_u_x(J, smt, x0, (c), (k))
+
+__device__ __forceinline__ double tb_u_horner(const TbJets &J, const double *__restrict__ smt,
+                                              const double *__restrict__ x0, const int c, const double dt) {
+    double s = TB_X(c, TB_P);
+#pragma unroll
+    for (int k = TB_P - 1; k >= 0; k--) s = A_(M_(s, dt), TB_X(c, k));
+    return s;
+}
+
+/* _second_stepsize on a local copy of one jet (cold path) */
+__device__ __noinline__ double tb_second_stepsize_arr(const double *x) {
+    bool allzero = true;
+    for (int k = 0; k <= TB_P; k++)
+        if (x[k] != 0.0) { allzero = false; break; }
+    if (allzero) return TB_INF;
+    double h = 0.0;
+    for (int k = 1; k <= TB_P - 2; k++) {
+        double aux = fabs(x[k]);
+        if (aux == 0.0) continue;
+        h = fmax(h, tb_stepsize_k(aux, 1.0, k));
+    }
+    return h;
+}
+
+/* stepsize + clamp (stepsize.jl:58-99, taylorstep.jl:79).  Fast mode with
+ * reltol == 0: min over components of (eps/|x_k|)^(1/k) = (eps/max_c|x_k|)^(1/k),
+ * so two logarithms and one exponential per step instead of 2*dof pow calls.     */
+__device__ __forceinline__ double tb_u_stepsize(const TbJets &J, const double *__restrict__ smt,
+                                                const double *__restrict__ x0, const TbArgs &a) {
+    double h = TB_INF;
+#if TB_MODE == 1
+    if (a.reltol == 0.0) {
+        double m1 = 0.0, m2 = 0.0;
+#pragma unroll
+        for (int c = 0; c < TB_DOF; c++) {
+            m1 = fmax(m1, fabs(TB_X(c, TB_P - 1)));
+            m2 = fmax(m2, fabs(TB_X(c, TB_P)));
+        }
+        const double le = log(a.abstol);
+        double l = TB_INF;
+        if (m1 != 0.0) l = fmin(l, (le - log(m1)) * (1.0 / (double)(TB_P - 1)));
+        if (m2 != 0.0) l = fmin(l, (le - log(m2)) * (1.0 / (double)TB_P));
+        if (l != TB_INF) h = exp(l);
+    } else
+#endif
+    {
+#pragma unroll
+        for (int c = 0; c < TB_DOF; c++) {
+            const double x0norm = fabs(TB_X(c, 0));
+#pragma unroll
+            for (int k = TB_P - 1; k <= TB_P; k++) {
+                const double aux = fabs(TB_X(c, k));
+                if (aux == 0.0) continue;
+                const double rel = M_(a.reltol, x0norm);
+                const double eps = (a.abstol >= rel) ? a.abstol : rel;
+                h = fmin(h, tb_stepsize_k(aux, eps, k));
+            }
+        }
+    }
+    if (h == TB_INF) { /* all last coefficients vanish: second step-size control */
+        h = 0.0;
+        double buf[TB_P + 1];
+#pragma unroll
+        for (int c = 0; c < TB_DOF; c++) {
+#pragma unroll
+            for (int k = 0; k <= TB_P; k++) buf[k] = TB_X(c, k);
+            h = fmax(h, tb_second_stepsize_arr(buf));
+        }
+    }
+    h = (h < a.minstep) ? a.minstep : ((h > a.maxstep) ? a.maxstep : h);
+    return h;
+}
+#endif /* TB_VARIANT == 2 */
 
 #if TB_KIND == 2
 /* modifiedGS!(A, Q, R): src/lyapunovspectrum.jl:118-146, column-major n x n;
@@ -174,8 +262,10 @@ __device__ __forceinline__ bool tb_isfinite_state(const double *x0) {
 
 /* update_cache!: src/integrator/cache.jl:435-442 */
 __device__ __forceinline__ void tb_update_cache(double *__restrict__ smt, const double *x0) {
+#if TB_VARIANT == 1
 #pragma unroll
     for (int c = 0; c < TB_NX; c++) S(c, 0) = x0[c];
+#endif /* variant 2: tb_u_jets reads x0 directly */
 }
 
 /* returns true when the trajectory needs no step at all */
@@ -236,6 +326,27 @@ __device__ __forceinline__ bool tb_traj_init(TbTraj &T, double *__restrict__ smt
     return !(M_(T.sign, T.t0) < M_(T.sign, T.tmax));
 }
 
+/* variant-independent spelling of "the jets of the current step" */
+#if TB_VARIANT == 1
+#define TB_JETS_DECL
+#define TB_JETS_ARGS smt
+#define TB_JETS_PARAMS const double *__restrict__ smt
+#define TB_COMPUTE_JETS(T) tb_jetcoeffs(smt, (T).par, (T).t0)
+#define TB_STEPSIZE(a) tb_stepsize(smt, (a))
+#define TB_HORNER(c, dt) tb_horner(smt, (c), (dt))
+#define TB_XCOEF(c, k) S((c), (k))
+#define TB_UNROLL_V2
+#else
+#define TB_JETS_DECL TbJets J; const double *x0 = T.x0;
+#define TB_JETS_ARGS J, smt, x0
+#define TB_JETS_PARAMS const TbJets &J, const double *__restrict__ smt, const double *__restrict__ x0
+#define TB_COMPUTE_JETS(T) tb_u_jets(J, smt, (T).par, (T).t0, x0)
+#define TB_STEPSIZE(a) tb_u_stepsize(J, smt, x0, (a))
+#define TB_HORNER(c, dt) tb_u_horner(J, smt, x0, (c), (dt))
+#define TB_XCOEF(c, k) TB_X((c), (k))
+#define TB_UNROLL_V2 _Pragma("unroll")
+#endif
+
 __device__ __forceinline__ void tb_store_step(const TbTraj &T, const double *__restrict__ smt, const TbArgs &a) {
     /* called after nsteps += 1: column nsteps-1 */
     const long long s = T.nsteps - 1, N = a.N;
@@ -247,35 +358,46 @@ __device__ __forceinline__ void tb_store_step(const TbTraj &T, const double *__r
     }
 }
 /* set_psol!: src/integrator/taylorinteg.jl:176-186 (polynomial of the step just taken) */
-__device__ __forceinline__ void tb_store_psol(const TbTraj &T, const double *__restrict__ smt, const TbArgs &a) {
+__device__ __forceinline__ void tb_store_psol(const TbTraj &T, TB_JETS_PARAMS, const TbArgs &a) {
     const long long s = T.nsteps - 1, N = a.N;
-    if (a.psol && s < a.stride)
-        for (int c = 0; c < TB_DOF; c++)
-            for (int k = 0; k <= TB_P; k++) a.psol[(((long long)c * TB_NP1 + k) * a.stride + s) * N + T.i] = S(c, k);
+    if (a.psol && s < a.stride) {
+        TB_UNROLL_V2
+        for (int c = 0; c < TB_DOF; c++) {
+            TB_UNROLL_V2
+            for (int k = 0; k <= TB_P; k++)
+                a.psol[(((long long)c * TB_NP1 + k) * a.stride + s) * N + T.i] = TB_XCOEF(c, k);
+        }
+    }
 }
 
 /* One iteration of the driver loop; returns true when the trajectory is done. */
 __device__ __forceinline__ bool tb_traj_step(TbTraj &T, double *__restrict__ smt, const TbArgs &a) {
 #if TB_KIND == 0
     /* taylorinteg!: src/integrator/taylorinteg.jl:356-378 (t0,tmax) and 607-639 (trange) */
-    tb_jetcoeffs(smt, T.par, T.t0);
-    double dt = tb_stepsize(smt, a);
+    TB_JETS_DECL
+    TB_COMPUTE_JETS(T);
+    double dt = TB_STEPSIZE(a);
     if (dt == 0.0) { T.st |= TB_ST_ZERO_STEP; return true; }
     const double rem = B_(T.tmax, T.t0);
     dt = M_(T.sign, fmin(dt, M_(T.sign, rem)));
+    double xn[TB_DOF];
 #pragma unroll
-    for (int c = 0; c < TB_DOF; c++) T.x0[c] = tb_horner(smt, c, dt);
+    for (int c = 0; c < TB_DOF; c++) xn[c] = TB_HORNER(c, dt);
     if (a.trange) {
         const double tnext = A_(T.t0, dt);
         const long long N = a.N;
         while (M_(T.sign, T.t1) < M_(T.sign, tnext)) {
             const double d1 = B_(T.t1, T.t0);
-            if (a.xv_trange)
+            if (a.xv_trange) {
+                TB_UNROLL_V2
                 for (int c = 0; c < TB_DOF; c++)
-                    a.xv_trange[((long long)c * a.nt + (T.iter - 1)) * N + T.i] = tb_horner(smt, c, d1);
+                    a.xv_trange[((long long)c * a.nt + (T.iter - 1)) * N + T.i] = TB_HORNER(c, d1);
+            }
             T.iter += 1;
             T.t1 = a.trange[T.iter - 1];
         }
+#pragma unroll
+        for (int c = 0; c < TB_DOF; c++) T.x0[c] = xn[c];
         if (dt == rem) {
             if (a.xv_trange)
                 for (int c = 0; c < TB_DOF; c++) a.xv_trange[((long long)c * a.nt + (T.iter - 1)) * N + T.i] = T.x0[c];
@@ -286,7 +408,9 @@ __device__ __forceinline__ bool tb_traj_step(TbTraj &T, double *__restrict__ smt
         tb_update_cache(smt, T.x0);
         T.nsteps += 1;
     } else {
-        tb_store_psol(T, smt, a);
+        tb_store_psol(T, TB_JETS_ARGS, a);
+#pragma unroll
+        for (int c = 0; c < TB_DOF; c++) T.x0[c] = xn[c];
         T.t0 = A_(T.t0, dt);
         tb_update_cache(smt, T.x0);
         T.nsteps += 1;
@@ -305,7 +429,7 @@ __device__ __forceinline__ bool tb_traj_step(TbTraj &T, double *__restrict__ smt
     T.dt = dt;
 #pragma unroll
     for (int c = 0; c < TB_DOF; c++) T.x0[c] = tb_horner(smt, c, dt);
-    tb_store_psol(T, smt, a);
+    tb_store_psol(T, TB_JETS_ARGS, a);
     const bool f_now = tb_eval_event(smt, T.par, T.t0);
     const double g_now = TB_EV_G(eo);
     if (T.f_old && f_now && (M_(T.g_old, g_now) < 0.0)) { /* surfacecrossing: rootfinding.jl:124-132 */
@@ -451,13 +575,23 @@ extern "C" __global__ void __launch_bounds__(TB_BT, TB_MINB) tb_jet_kernel(const
     for (long long i = (long long)blockIdx.x * TB_BT + threadIdx.x; i < a.N; i += (long long)gridDim.x * TB_BT) {
         double par[TB_NPAR > 0 ? TB_NPAR : 1];
         for (int j = 0; j < TB_NPAR; j++) par[j] = a.params_per_traj ? a.params[(long long)j * a.N + i] : a.params[j];
-        for (int c = 0; c < TB_DOF; c++) S(c, 0) = a.q0[(long long)c * a.N + i];
-        tb_jetcoeffs(smt, par, a.t0);
-        double dt = tb_stepsize(smt, a);
+        struct { double x0[TB_DOF]; double par[TB_NPAR > 0 ? TB_NPAR : 1]; double t0; } T;
+        for (int j = 0; j < TB_NPAR; j++) T.par[j] = par[j];
+        T.t0 = a.t0;
+#pragma unroll
+        for (int c = 0; c < TB_DOF; c++) T.x0[c] = a.q0[(long long)c * a.N + i];
+        tb_update_cache(smt, T.x0);
+        TB_JETS_DECL
+        TB_COMPUTE_JETS(T);
+        double dt = TB_STEPSIZE(a);
         if (a.dtout) a.dtout[i] = dt;
-        if (a.xjet)
-            for (int c = 0; c < TB_DOF; c++)
-                for (int k = 0; k <= TB_P; k++) a.xjet[((long long)c * TB_NP1 + k) * a.N + i] = S(c, k);
+        if (a.xjet) {
+            TB_UNROLL_V2
+            for (int c = 0; c < TB_DOF; c++) {
+                TB_UNROLL_V2
+                for (int k = 0; k <= TB_P; k++) a.xjet[((long long)c * TB_NP1 + k) * a.N + i] = TB_XCOEF(c, k);
+            }
+        }
     }
 }
 

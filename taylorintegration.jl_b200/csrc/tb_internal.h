@@ -29,6 +29,10 @@ struct Layout {
 };
 
 int generate(const Ode &ode, const tb_compile_opts_t &co, Layout &L, std::string &src, std::string &err);
+/* variant 2: fully unrolled, register-tiled (tb_codegen_unrolled.cpp); TB_ERR_UNSUPPORTED when it does not apply */
+int generate_unrolled(const Ode &ode, const tb_compile_opts_t &co, Layout &L, std::string &src, std::string &err);
+/* picks the generator: variant 2 where it applies unless TB_CF_ROLLED is set */
+int generate_any(const Ode &ode, const tb_compile_opts_t &co, Layout &L, std::string &src, std::string &err);
 
 /* device source text embedded at build time (tools/embed.py -> tb_embedded.inc) */
 const char *embedded_math_h();

@@ -455,7 +455,7 @@ const char *tb_generate_source(const tb_ode_t *ode, const tb_compile_opts_t *co)
     if (!ode || !co) { set_error("tb_generate_source: NULL argument"); return nullptr; }
     Layout L;
     std::string err;
-    if (generate(ode->o, *co, L, src, err) != TB_OK) { set_error("tb_generate_source: " + err); return nullptr; }
+    if (generate_any(ode->o, *co, L, src, err) != TB_OK) { set_error("tb_generate_source: " + err); return nullptr; }
     return src.c_str();
 }
 
@@ -467,7 +467,7 @@ tb_kernel_t *tb_compile(const tb_ode_t *ode, const tb_compile_opts_t *co) {
     k->ode.desc.jac = k->ode.desc.has_jac ? k->ode.jac.data() : nullptr;
     k->co = *co;
     std::string err;
-    if (generate(k->ode, k->co, k->L, k->source, err) != TB_OK) {
+    if (generate_any(k->ode, k->co, k->L, k->source, err) != TB_OK) {
         set_error("tb_compile: " + err);
         delete k;
         return nullptr;

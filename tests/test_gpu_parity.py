@@ -3,6 +3,7 @@ seeded inputs.  Floating-point bar (BASELINE.json north_star): first-step coeffi
 2 ulp, final states within 1e-12 relative, Lyapunov exponents within 1e-6.  Parity mode is built to be
 bit-identical to the oracle (same operations in the same order, shared elementary functions), so these tests
 assert exact equality and would catch any drift long before the stated tolerances."""
+import mpmath as mp
 import numpy as np
 import pytest
 
@@ -13,6 +14,7 @@ from taylorintegration_b200 import cos, exp, log, sin, sqrt
 
 pytestmark = pytest.mark.gpu
 T_PEND = 7.019250311844546
+mp.mp.prec = 200
 
 
 def _ulps(a, b):
@@ -28,8 +30,10 @@ def test_first_step_jets_and_stepsize_kepler():
         xo, _, dto = oracle.jet(tape, 28, q0[:, i], mu)
         assert np.array_equal(xj[:, :, i], xo)           # bar: <= 2 ulp
         assert dt[i] == dto
-        xl, _, dtl = oracle.jet(tape, 28, q0[:, i], mu, math=oracle.MATH_LIBM)  # libm pow/sincos instead of tb_math
-        assert _ulps(dt[i], dtl) <= 2
+        # step size from the GPU's own coefficients in 200-bit arithmetic: (eps/|x_k|)^(1/k), stepsize.jl:107-111
+        want = min(mp.power(mp.mpf(1e-20) / abs(mp.mpf(float(xj[c, kk, i]))), mp.mpf(1) / kk)
+                   for c in range(4) for kk in (27, 28) if xj[c, kk, i] != 0.0)
+        assert abs(mp.mpf(float(dt[i])) - want) <= 2 * mp.mpf(float(np.spacing(dt[i])))
 
 
 def test_xsquared_goldens_on_gpu():
