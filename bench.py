@@ -44,6 +44,9 @@ def parse_args():
     ap.add_argument("--cpu-seconds", type=float, default=15.0, help="target CPU time of the cpu_baseline sample")
     ap.add_argument("--no-cpu-baseline", action="store_true")
     ap.add_argument("--no-e2e", action="store_true")
+    ap.add_argument("--reg-budget", type=int, default=0, help="doubles of jet storage in registers (kernel variant 2)")
+    ap.add_argument("--block-threads", type=int, default=0)
+    ap.add_argument("--kflags", type=int, default=0, help="TB_CF_* compile flags (4 = rolled variant 1)")
     return ap.parse_args()
 
 
@@ -169,7 +172,8 @@ def run_b200(a):
     dev = torch.device("cuda", local)
     tape, q0, mu, w = workload(a)
     N, dof = a.ntraj, 4
-    k = tb.Kernel(tape, a.order, L.KIND_PLAIN, L.MODE_PARITY if a.mode == "parity" else L.MODE_FAST)
+    k = tb.Kernel(tape, a.order, L.KIND_PLAIN, L.MODE_PARITY if a.mode == "parity" else L.MODE_FAST,
+                  reg_budget=a.reg_budget, block_threads=a.block_threads, flags=a.kflags)
     opts = tb.make_opts(abstol=w["abstol"], maxsteps=w["maxsteps"])
     # pinned host buffers (e2e arm) and device-resident copies (kernel arm)
     h_q0 = torch.from_numpy(q0).pin_memory()

@@ -263,7 +263,10 @@ struct UGen {
                     else e.line("  const double %s = D_(%s, %s);", r, A(k).c_str(), B(k).c_str());
                 } else if (k0) {
                     if (fast) { e.line("  const double inv%d = 1.0 / %s;", opi, B(0).c_str()); e.line("  const double %s = %s * inv%d;", r, A(0).c_str(), opi); }
-                    else e.line("  const double %s = D_(%s, %s);", r, A(0).c_str(), B(0).c_str());
+                    else {
+                        e.line("  const double den%d = %s, inv%d = D_(1.0, den%d); const bool ok%d = tb_midrange(den%d);", opi, B(0).c_str(), opi, opi, opi, opi);
+                        e.line("  const double %s = D_(%s, den%d);", r, A(0).c_str(), opi);
+                    }
                 } else {
                     Terms t;
                     for (int i = 0; i <= k - 1; i++) term(t, C(i), B(k - i));
@@ -272,8 +275,8 @@ struct UGen {
                         if (sa) e.line("  const double %s = -%s * inv%d;", r, s.c_str(), opi);
                         else e.line("  const double %s = (%s - %s) * inv%d;", r, A(k).c_str(), s.c_str(), opi);
                     } else {
-                        if (sa) e.line("  const double %s = D_(N_(%s), %s);", r, s.c_str(), B(0).c_str());
-                        else e.line("  const double %s = D_(B_(%s, %s), %s);", r, A(k).c_str(), s.c_str(), B(0).c_str());
+                        if (sa) e.line("  const double %s = tb_div_y(N_(%s), den%d, inv%d, ok%d);", r, s.c_str(), opi, opi, opi);
+                        else e.line("  const double %s = tb_div_y(B_(%s, %s), den%d, inv%d, ok%d);", r, A(k).c_str(), s.c_str(), opi, opi, opi);
                     }
                 }
                 break;
@@ -281,6 +284,7 @@ struct UGen {
                 if (k0) {
                     e.line("  const double %s = Q_(%s);", r, A(0).c_str());
                     if (fast) e.line("  const double inv%d = 0.5 / %s;", opi, r);
+                    else e.line("  const double den%d = M_(2.0, %s), inv%d = D_(1.0, den%d); const bool ok%d = tb_midrange(den%d);", opi, r, opi, opi, opi, opi);
                 } else {
                     const int kodd = k & 1, kend = (k - 2 + kodd) / 2;
                     Terms t;
@@ -292,7 +296,7 @@ struct UGen {
                     } else {
                         std::string aux = fmt("B_(%s, M_(2.0, %s))", A(k).c_str(), s.c_str());
                         if (!kodd) aux = fmt("B_(%s, M_(%s, %s))", aux.c_str(), C(kend + 1).c_str(), C(kend + 1).c_str());
-                        e.line("  const double %s = D_(%s, M_(2.0, %s));", r, aux.c_str(), C(0).c_str());
+                        e.line("  const double %s = tb_div_y(%s, den%d, inv%d, ok%d);", r, aux.c_str(), opi, opi, opi);
                     }
                 }
                 break;
@@ -330,7 +334,7 @@ struct UGen {
                     }
                     std::string s = sum(e, t);
                     if (fast) e.line("  const double %s = %s * %s;", r, s.c_str(), dlit(1.0 / k).c_str());
-                    else e.line("  const double %s = D_(%s, %s);", r, s.c_str(), dlit((double)k).c_str());
+                    else e.line("  const double %s = %s;", r, divc(s, k).c_str());
                 }
                 break;
             case TB_OP_LOG:
@@ -344,7 +348,7 @@ struct UGen {
                     for (int i = 2; i <= k - 1; i++) term(t, fmt("M_(%s, %s)", dlit((double)(k - i)).c_str(), A(i).c_str()), C(k - i));
                     std::string s = sum(e, t);
                     if (fast) e.line("  const double %s = fma(-%s, %s, %s) * inv%d;", r, s.c_str(), dlit(1.0 / k).c_str(), A(k).c_str(), opi);
-                    else e.line("  const double %s = D_(B_(%s, D_(%s, %s)), %s);", r, A(k).c_str(), s.c_str(), dlit((double)k).c_str(), A(0).c_str());
+                    else e.line("  const double %s = D_(B_(%s, %s), %s);", r, A(k).c_str(), divc(s, k).c_str(), A(0).c_str());
                 }
                 break;
             case TB_OP_SINCOS: {
@@ -369,8 +373,8 @@ struct UGen {
                         e.line("  const double %s = %s * %s;", r, s1.c_str(), dlit(1.0 / k).c_str());
                         e.line("  const double %s = %s * %s;", RC.c_str(), s2.c_str(), dlit(1.0 / k).c_str());
                     } else {
-                        e.line("  const double %s = D_(%s, %s);", r, s1.c_str(), dlit((double)k).c_str());
-                        e.line("  const double %s = D_(%s, %s);", RC.c_str(), s2.c_str(), dlit((double)k).c_str());
+                        e.line("  const double %s = %s;", r, divc(s1, k).c_str());
+                        e.line("  const double %s = %s;", RC.c_str(), divc(s2, k).c_str());
                     }
                 }
                 store(e, op.aux, k, RC);
@@ -381,6 +385,13 @@ struct UGen {
         }
         store(e, op.res, k, R);
         defined.insert(op.res);
+    }
+
+    /* parity-mode x / n for a small integer constant n: exact multiply for powers of two,
+     * Markstein correction (tb_div_y) otherwise -- same bits as the IEEE division      */
+    std::string divc(const std::string &x, int n) {
+        if ((n & (n - 1)) == 0) return fmt("M_(%s, %s)", x.c_str(), dlit(1.0 / n).c_str());
+        return fmt("tb_div_y(%s, %s, %s, true)", x.c_str(), dlit((double)n).c_str(), dlit(1.0 / n).c_str());
     }
 
     void store(Em &e, int32_t o, int k, const std::string &v) {
@@ -409,7 +420,7 @@ struct UGen {
                 if (!defined.count(dx)) { err = "tape does not define dx[" + std::to_string(c) + "]"; return; }
                 std::string v = fmt("vX%d_%d", c, k + 1);
                 if (fast) e.line("  const double %s = %s * %s;", v.c_str(), vname(dx, k).c_str(), dlit(1.0 / (k + 1)).c_str());
-                else e.line("  const double %s = D_(%s, %s);", v.c_str(), vname(dx, k).c_str(), dlit((double)(k + 1)).c_str());
+                else e.line("  const double %s = %s;", v.c_str(), divc(vname(dx, k), k + 1).c_str());
                 store(e, TB_OPERAND(TB_K_X, c), k + 1, v);
             }
         }

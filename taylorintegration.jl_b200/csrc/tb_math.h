@@ -213,18 +213,27 @@ TB_HD double tb_log(double x) {
     return L.hi;
 }
 
-/* x^y for x >= 0 (the cases the integrator meets: (eps/|x_k|)^(1/k), r2^1.5) */
+/* x^y; x < 0 only with integer y (the cases the integrator meets: (eps/|x_k|)^(1/k), r2^1.5, x^3.0) */
 TB_HD double tb_pow(double x, double y) {
     if (x != x || y != y) return TB_ADD(x, y);
     if (y == 0.0) return 1.0;
     if (x == 0.0) return (y > 0.0) ? 0.0 : TB_FROM_BITS(0x7FF0000000000000ull);
-    if (x < 0.0) return TB_FROM_BITS(0x7FF8000000000000ull);
-    if (TB_TO_BITS(x) == 0x7FF0000000000000ull) return (y > 0.0) ? x : 0.0;
-    if (x == 1.0) return 1.0;
+    double sgn = 1.0;
+    if (x < 0.0) { /* negative base: defined for integer exponents only (Julia: DomainError otherwise) */
+        if (TB_ABS(y) >= 9007199254740992.0) { x = -x; }
+        else {
+            const long long n = (long long)y;
+            if ((double)n != y) return TB_FROM_BITS(0x7FF8000000000000ull);
+            if (n & 1) sgn = -1.0;
+            x = -x;
+        }
+    }
+    if (TB_TO_BITS(x) == 0x7FF0000000000000ull) return (y > 0.0) ? TB_MUL(sgn, x) : 0.0;
+    if (x == 1.0) return sgn;
     tb_dd L = tb_log_dd(x);
     tb_dd p = tb_two_prod(y, L.hi);
     p.lo = TB_FMA(y, L.lo, p.lo);
-    return tb_exp_dd(p.hi, p.lo);
+    return TB_MUL(sgn, tb_exp_dd(p.hi, p.lo));
 }
 
 /* ---- sin / cos --------------------------------------------------------------

@@ -36,6 +36,8 @@ def test_pow_exp_log_ulp():
         for y in (1 / 27, 1 / 28, 1.5, 1 / 25, 1 / 24):
             m = max(m, _ulp_err(o.tbo_math_pow(float(x), y), mp.power(mp.mpf(float(x)), mp.mpf(y))))
     assert m < 0.6, m
+    assert o.tbo_math_pow(-0.9, 3.0) == -o.tbo_math_pow(0.9, 3.0) and o.tbo_math_pow(-2.0, 2.0) == 4.0
+    assert np.isnan(o.tbo_math_pow(-2.0, 0.5))
     m = 0.0
     for x in rng.uniform(-700, 700, 3000):
         m = max(m, _ulp_err(o.tbo_math_exp(float(x)), mp.exp(mp.mpf(float(x)))))
