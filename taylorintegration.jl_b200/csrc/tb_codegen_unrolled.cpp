@@ -135,263 +135,416 @@ struct UGen {
         }
     }
 
-    /* ---- operand access ------------------------------------------------------ */
-    std::string sref(int32_t o, int idx) {
-        auto it = ser.find(o);
+    /* ---- values ---------------------------------------------------------------
+     * A coefficient (series o, index idx) is referred to by the NAME of the local
+     * that computed it while idx >= cur (the lowest order with unfinished tape
+     * entries: such values are still in registers), and re-read from its storage
+     * (register array or one LDS.64) afterwards.  Loads are cached per emission
+     * group, so a coefficient shared by the chains of a group is read once.      */
+    struct Ref { int32_t o; int idx; };
+    typedef std::pair<int32_t, int> Key;
+    std::set<Key> computed;
+    std::map<Key, std::string> loaded;
+    std::map<std::pair<std::string, std::string>, std::string> scaled;
+    int cur = 0;
+
+    static std::string vname(int32_t o, int k) {
+        int kind = TB_OPERAND_KIND(o), i = TB_OPERAND_INDEX(o);
+        return fmt("%s%d_%d", kind == TB_K_DX ? "vD" : (kind == TB_K_TMP ? "vT" : "vX"), i, k);
+    }
+    bool avail(const Ref &r) const {
+        if (TB_OPERAND_KIND(r.o) == TB_K_TIME) return true;
+        return computed.count(Key(r.o, r.idx)) != 0;
+    }
+    std::string val(Em &e, const Ref &r) {
+        if (TB_OPERAND_KIND(r.o) == TB_K_TIME) return r.idx == 0 ? "t0" : (r.idx == 1 ? "1.0" : "0.0");
+        if (!computed.count(Key(r.o, r.idx))) { err = "internal: coefficient read before it is computed"; return "0.0"; }
+        if (r.idx >= cur) return vname(r.o, r.idx);
+        auto it = ser.find(r.o);
         if (it == ser.end() || it->second.place == PL_NONE || it->second.place == PL_DERIVED) {
             err = "internal: series operand not stored";
             return "0.0";
         }
-        if (it->second.place == PL_REG) return fmt("J.r%d[%d]", it->second.id, idx);
-        return fmt("S(%d, %d)", it->second.id, idx);
-    }
-    static std::string vname(int32_t o, int k) {
-        int kind = TB_OPERAND_KIND(o), i = TB_OPERAND_INDEX(o);
-        return fmt("%s%d_%d", kind == TB_K_DX ? "vD" : (kind == TB_K_TMP ? "vT" : "vX"), i, k);
+        if (it->second.place == PL_REG) return fmt("J.r%d[%d]", it->second.id, r.idx);
+        auto lt = loaded.find(Key(r.o, r.idx));
+        if (lt != loaded.end()) return lt->second;
+        std::string n = fmt("l%d", tmpc++);
+        e.line("  const double %s = S(%d, %d);", n.c_str(), it->second.id, r.idx);
+        loaded[Key(r.o, r.idx)] = n;
+        return n;
     }
     std::string num(int32_t o, const tb_op_t &op) const {
         if (TB_OPERAND_KIND(o) == TB_K_PAR) return fmt("par[%d]", TB_OPERAND_INDEX(o));
         return dlit(op.imm);
     }
-    /* value of series operand o at static index idx while generating order k */
-    std::string rd(int32_t o, int idx, int k, const std::set<int32_t> &defined) {
-        int kind = TB_OPERAND_KIND(o);
-        if (kind == TB_K_TIME) return idx == 0 ? "t0" : (idx == 1 ? "1.0" : "0.0");
-        if (idx == k && (kind == TB_K_X || defined.count(o))) return vname(o, k);
-        return sref(o, idx);
+    void define(Em &e, int32_t o, int k, const std::string &name) {
+        store(e, o, k, name);
+        computed.insert(Key(o, k));
     }
-    bool is_zero_time(int32_t o, int idx) const { return TB_OPERAND_KIND(o) == TB_K_TIME && idx >= 2; }
-
-    /* sum of products.  Parity: c = t0; c = c + t1; ... with unfused ops, in order.
-     * Fast: up to 4 partial accumulators, FMA.  Each term = (x, y) meaning x*y;
-     * `neg` subtracts the products instead (sincos cosine chain).                 */
-    std::string sum(Em &e, const std::vector<std::pair<std::string, std::string>> &t, bool neg_chain = false) {
-        std::string acc = fmt("a%d", tmpc++);
-        if (t.empty()) { e.line("  const double %s = 0.0;", acc.c_str()); return acc; }
-        if (!fast) {
-            if (neg_chain) e.line("  double %s = M_(N_(%s), %s);", acc.c_str(), t[0].first.c_str(), t[0].second.c_str());
-            else e.line("  double %s = M_(%s, %s);", acc.c_str(), t[0].first.c_str(), t[0].second.c_str());
-            for (size_t i = 1; i < t.size(); i++)
-                e.line("  %s = %s(%s, M_(%s, %s));", acc.c_str(), neg_chain ? "B_" : "A_", acc.c_str(), t[i].first.c_str(), t[i].second.c_str());
-            return acc;
+    static int eff_op(const tb_op_t &op) {
+        if (op.op != TB_OP_POW) return op.op;
+        if (op.imm == 0.0) return TB_OP_ONE;
+        if (op.imm == 1.0) return TB_OP_IDENTITY;
+        if (op.imm == 2.0) return TB_OP_SQR;
+        if (op.imm == 0.5) return TB_OP_SQRT;
+        return TB_OP_POW;
+    }
+    /* does entry `op` at order k run a recurrence sum? */
+    static bool is_sum_node(const tb_op_t &op, int k) {
+        if (k == 0) return false;
+        const bool sa = u_is_num(op.a), sb = u_is_num(op.b);
+        switch (eff_op(op)) {
+            case TB_OP_MUL: return !sa && !sb;
+            case TB_OP_DIV: return !sb;
+            case TB_OP_SQR: case TB_OP_SQRT: case TB_OP_POW: case TB_OP_EXP: case TB_OP_SINCOS: return true;
+            case TB_OP_LOG: return k >= 2;
+            default: return false;
         }
-        const int nacc = (int)std::min<size_t>(4, t.size());
-        for (int j = 0; j < nacc; j++)
-            e.line("  double %s_%d = %s * %s;", acc.c_str(), j, t[j].first.c_str(), t[j].second.c_str());
-        for (size_t i = nacc; i < t.size(); i++)
-            e.line("  %s_%d = fma(%s, %s, %s_%d);", acc.c_str(), (int)(i % nacc), t[i].first.c_str(), t[i].second.c_str(), acc.c_str(), (int)(i % nacc));
-        std::string comb;
-        if (nacc == 1) comb = fmt("%s_0", acc.c_str());
-        else if (nacc == 2) comb = fmt("%s_0 + %s_1", acc.c_str(), acc.c_str());
-        else if (nacc == 3) comb = fmt("(%s_0 + %s_1) + %s_2", acc.c_str(), acc.c_str(), acc.c_str());
-        else comb = fmt("(%s_0 + %s_1) + (%s_2 + %s_3)", acc.c_str(), acc.c_str(), acc.c_str(), acc.c_str());
-        e.line("  const double %s = %s(%s);", acc.c_str(), neg_chain ? "-" : "", comb.c_str());
-        return acc;
+    }
+    /* coefficients entry `op` reads at order k (conservative full ranges) */
+    void deps(const tb_op_t &op, int k, std::vector<Ref> &out) const {
+        const bool sa = u_is_num(op.a), sb = u_is_num(op.b);
+        auto range = [&](int32_t o, int lo, int hi) { if (u_is_series(o)) for (int i = lo; i <= hi; i++) out.push_back({o, i}); };
+        switch (eff_op(op)) {
+            case TB_OP_IDENTITY: case TB_OP_NEG: if (!sa) range(op.a, k, k); break;
+            case TB_OP_ZERO: case TB_OP_ONE: break;
+            case TB_OP_ADD: case TB_OP_SUB: if (!sa) range(op.a, k, k); if (!sb) range(op.b, k, k); break;
+            case TB_OP_MUL:
+                if (sa && sb) break;
+                if (sa) range(op.b, k, k); else if (sb) range(op.a, k, k);
+                else { range(op.a, 0, k); range(op.b, 0, k); }
+                break;
+            case TB_OP_SQR: range(op.a, 0, k); break;
+            case TB_OP_DIV:
+                if (sa && sb) break;
+                if (sb) { range(op.a, k, k); break; }
+                range(op.b, 0, k); if (!sa) range(op.a, k, k); range(op.res, 0, k - 1);
+                break;
+            case TB_OP_SQRT: range(op.a, k, k); range(op.res, 0, k - 1); break;
+            case TB_OP_POW: case TB_OP_EXP: case TB_OP_LOG: range(op.a, 0, k); range(op.res, 0, k - 1); break;
+            case TB_OP_SINCOS: range(op.a, 0, k); range(op.res, 0, k - 1); range(op.aux, 0, k - 1); break;
+            default: break;
+        }
+    }
+    /* ready: every dependency computed, ignoring coefficients `skip_k` of the entry's own outputs */
+    bool node_ready(const tb_op_t &op, int k, int skip_k = -1) const {
+        std::vector<Ref> d;
+        deps(op, k, d);
+        for (const Ref &r : d) {
+            if (skip_k >= 0 && r.idx == skip_k && (r.o == op.res || (op.op == TB_OP_SINCOS && r.o == op.aux))) continue;
+            if (!avail(r)) return false;
+        }
+        return true;
     }
 
-    typedef std::vector<std::pair<std::string, std::string>> Terms;
-    void term(Terms &t, const std::string &x, const std::string &y) {
-        if (fast && (x == "0.0" || y == "0.0")) return; /* structural zeros of the time series */
-        t.push_back({x, y});
-    }
-
-    /* one tape entry at static order k */
-    void emit_op(Em &e, int opi, const tb_op_t &op, int k, std::set<int32_t> &defined) {
+    /* ---- entries without a recurrence sum: order 0 of everything, linear ops, log at k = 1 ---- */
+    void emit_cheap(Em &e, int opi, const tb_op_t &op, int k) {
         const bool sa = u_is_num(op.a), sb = u_is_num(op.b);
         const bool k0 = k == 0;
         const std::string R = vname(op.res, k);
-        auto A = [&](int idx) { return sa ? num(op.a, op) : rd(op.a, idx, k, defined); };
-        auto B = [&](int idx) { return sb ? num(op.b, op) : rd(op.b, idx, k, defined); };
-        auto C = [&](int idx) { return rd(op.res, idx, k, defined); };
         const char *r = R.c_str();
-        int opc = op.op;
         const double pw = op.imm;
-        if (opc == TB_OP_POW) {
-            if (pw == 0.0) opc = TB_OP_ONE;
-            else if (pw == 1.0) opc = TB_OP_IDENTITY;
-            else if (pw == 2.0) opc = TB_OP_SQR;
-            else if (pw == 0.5) opc = TB_OP_SQRT;
-        }
-        switch (opc) {
+        /* operand strings are resolved first: val() may emit a load line */
+        auto A = [&](int idx) { return sa ? num(op.a, op) : val(e, {op.a, idx}); };
+        auto B = [&](int idx) { return sb ? num(op.b, op) : val(e, {op.b, idx}); };
+        switch (eff_op(op)) {
             case TB_OP_IDENTITY:
                 if (sa) e.line("  const double %s = %s;", r, k0 ? A(0).c_str() : "0.0");
-                else e.line("  const double %s = %s;", r, A(k).c_str());
+                else { std::string a = A(k); e.line("  const double %s = %s;", r, a.c_str()); }
                 break;
-            case TB_OP_NEG: e.line("  const double %s = N_(%s);", r, A(k).c_str()); break;
+            case TB_OP_NEG: { std::string a = A(k); e.line("  const double %s = N_(%s);", r, a.c_str()); break; }
             case TB_OP_ZERO: e.line("  const double %s = 0.0;", r); break;
             case TB_OP_ONE: e.line("  const double %s = %s;", r, k0 ? "1.0" : "0.0"); break;
             case TB_OP_ADD:
             case TB_OP_SUB: {
-                const char *F = opc == TB_OP_ADD ? "A_" : "B_";
-                if (sa && sb) { if (k0) e.line("  const double %s = %s(%s, %s);", r, F, A(0).c_str(), B(0).c_str()); else e.line("  const double %s = 0.0;", r); }
+                const bool add = eff_op(op) == TB_OP_ADD;
+                const char *F = add ? "A_" : "B_";
+                if (k0 || (!sa && !sb)) {
+                    if (sa && sb && !k0) { e.line("  const double %s = 0.0;", r); break; }
+                    std::string a = A(k), b = B(k);
+                    e.line("  const double %s = %s(%s, %s);", r, F, a.c_str(), b.c_str());
+                } else if (sa && sb) e.line("  const double %s = 0.0;", r);
                 else if (sa) {
-                    if (k0) e.line("  const double %s = %s(%s, %s);", r, F, A(0).c_str(), B(0).c_str());
-                    else if (opc == TB_OP_ADD) e.line("  const double %s = %s;", r, B(k).c_str());
-                    else e.line("  const double %s = N_(%s);", r, B(k).c_str());
-                } else if (sb) {
-                    if (k0) e.line("  const double %s = %s(%s, %s);", r, F, A(0).c_str(), B(0).c_str());
-                    else e.line("  const double %s = %s;", r, A(k).c_str());
-                } else e.line("  const double %s = %s(%s, %s);", r, F, A(k).c_str(), B(k).c_str());
+                    std::string b = B(k);
+                    if (add) e.line("  const double %s = %s;", r, b.c_str());
+                    else e.line("  const double %s = N_(%s);", r, b.c_str());
+                } else { std::string a = A(k); e.line("  const double %s = %s;", r, a.c_str()); }
                 break;
             }
             case TB_OP_MUL:
-                if (sa && sb) { if (k0) e.line("  const double %s = M_(%s, %s);", r, A(0).c_str(), B(0).c_str()); else e.line("  const double %s = 0.0;", r); }
-                else if (sa || sb) e.line("  const double %s = M_(%s, %s);", r, A(k).c_str(), B(k).c_str());
-                else {
-                    Terms t;
-                    for (int i = 0; i <= k; i++) term(t, A(i), B(k - i));
-                    std::string s = sum(e, t);
-                    e.line("  const double %s = %s;", r, s.c_str());
-                }
+                if (sa && sb && !k0) e.line("  const double %s = 0.0;", r);
+                else { std::string a = A(k), b = B(k); e.line("  const double %s = M_(%s, %s);", r, a.c_str(), b.c_str()); }
                 break;
-            case TB_OP_SQR:
-                if (k0) e.line("  const double %s = M_(%s, %s);", r, A(0).c_str(), A(0).c_str());
-                else {
-                    const int kodd = k & 1, kend = (k - 2 + kodd) / 2;
-                    Terms t;
-                    for (int i = 0; i <= kend; i++) term(t, A(i), A(k - i));
-                    std::string s = sum(e, t);
-                    if (kodd) e.line("  const double %s = M_(2.0, %s);", r, s.c_str());
-                    else if (fast) e.line("  const double %s = fma(%s, %s, 2.0 * %s);", r, A(k / 2).c_str(), A(k / 2).c_str(), s.c_str());
-                    else e.line("  const double %s = A_(M_(2.0, %s), M_(%s, %s));", r, s.c_str(), A(k / 2).c_str(), A(k / 2).c_str());
-                }
-                break;
+            case TB_OP_SQR: { std::string a = A(0); e.line("  const double %s = M_(%s, %s);", r, a.c_str(), a.c_str()); break; }
             case TB_OP_DIV:
-                if (sa && sb) { if (k0) e.line("  const double %s = D_(%s, %s);", r, A(0).c_str(), B(0).c_str()); else e.line("  const double %s = 0.0;", r); }
-                else if (sb) {
-                    if (fast) { if (k0) e.line("  const double inv%d = 1.0 / %s;", opi, B(0).c_str()); e.line("  const double %s = %s * inv%d;", r, A(k).c_str(), opi); }
-                    else e.line("  const double %s = D_(%s, %s);", r, A(k).c_str(), B(k).c_str());
-                } else if (k0) {
-                    if (fast) { e.line("  const double inv%d = 1.0 / %s;", opi, B(0).c_str()); e.line("  const double %s = %s * inv%d;", r, A(0).c_str(), opi); }
+                if (sa && sb) {
+                    if (k0) { std::string a = A(0), b = B(0); e.line("  const double %s = D_(%s, %s);", r, a.c_str(), b.c_str()); }
+                    else e.line("  const double %s = 0.0;", r);
+                } else if (sb) {
+                    std::string a = A(k), b = B(k);
+                    if (fast) { if (k0) e.line("  const double inv%d = 1.0 / %s;", opi, b.c_str()); e.line("  const double %s = %s * inv%d;", r, a.c_str(), opi); }
+                    else e.line("  const double %s = %s(%s, %s);", r, k0 ? "D_" : "DIVQ_", a.c_str(), b.c_str());
+                } else { /* k == 0 of a series divisor */
+                    std::string a = A(0), b = B(0);
+                    if (fast) { e.line("  const double inv%d = 1.0 / %s;", opi, b.c_str()); e.line("  const double %s = %s * inv%d;", r, a.c_str(), opi); }
                     else {
-                        e.line("  const double den%d = %s, inv%d = D_(1.0, den%d); const bool ok%d = tb_midrange(den%d);", opi, B(0).c_str(), opi, opi, opi, opi);
-                        e.line("  const double %s = D_(%s, den%d);", r, A(0).c_str(), opi);
-                    }
-                } else {
-                    Terms t;
-                    for (int i = 0; i <= k - 1; i++) term(t, C(i), B(k - i));
-                    std::string s = sum(e, t);
-                    if (fast) {
-                        if (sa) e.line("  const double %s = -%s * inv%d;", r, s.c_str(), opi);
-                        else e.line("  const double %s = (%s - %s) * inv%d;", r, A(k).c_str(), s.c_str(), opi);
-                    } else {
-                        if (sa) e.line("  const double %s = tb_div_y(N_(%s), den%d, inv%d, ok%d);", r, s.c_str(), opi, opi, opi);
-                        else e.line("  const double %s = tb_div_y(B_(%s, %s), den%d, inv%d, ok%d);", r, A(k).c_str(), s.c_str(), opi, opi, opi);
+                        e.line("  const double den%d = %s, inv%d = D_(1.0, den%d); const bool ok%d = tb_midrange(den%d); DENCHK_(den%d);", opi, b.c_str(), opi, opi, opi, opi, opi);
+                        e.line("  const double %s = D_(%s, den%d);", r, a.c_str(), opi);
                     }
                 }
                 break;
-            case TB_OP_SQRT:
-                if (k0) {
-                    e.line("  const double %s = Q_(%s);", r, A(0).c_str());
-                    if (fast) e.line("  const double inv%d = 0.5 / %s;", opi, r);
-                    else e.line("  const double den%d = M_(2.0, %s), inv%d = D_(1.0, den%d); const bool ok%d = tb_midrange(den%d);", opi, r, opi, opi, opi, opi);
-                } else {
-                    const int kodd = k & 1, kend = (k - 2 + kodd) / 2;
-                    Terms t;
-                    for (int i = 1; i <= kend; i++) term(t, C(i), C(k - i));
-                    std::string s = sum(e, t);
-                    if (fast) {
-                        if (kodd) e.line("  const double %s = fma(-2.0, %s, %s) * inv%d;", r, s.c_str(), A(k).c_str(), opi);
-                        else e.line("  const double %s = fma(-%s, %s, fma(-2.0, %s, %s)) * inv%d;", r, C(kend + 1).c_str(), C(kend + 1).c_str(), s.c_str(), A(k).c_str(), opi);
-                    } else {
-                        std::string aux = fmt("B_(%s, M_(2.0, %s))", A(k).c_str(), s.c_str());
-                        if (!kodd) aux = fmt("B_(%s, M_(%s, %s))", aux.c_str(), C(kend + 1).c_str(), C(kend + 1).c_str());
-                        e.line("  const double %s = tb_div_y(%s, den%d, inv%d, ok%d);", r, aux.c_str(), opi, opi, opi);
-                    }
-                }
+            case TB_OP_SQRT: {
+                std::string a = A(0);
+                e.line("  const double %s = Q_(%s);", r, a.c_str());
+                if (fast) e.line("  const double inv%d = 0.5 / %s;", opi, r);
+                else e.line("  const double den%d = M_(2.0, %s), inv%d = D_(1.0, den%d); const bool ok%d = tb_midrange(den%d); DENCHK_(den%d);", opi, r, opi, opi, opi, opi, opi);
                 break;
-            case TB_OP_POW:
-                if (k0) {
-                    e.line("  const double %s = tb_pow(%s, %s);", r, A(0).c_str(), dlit(pw).c_str());
-                    if (fast) e.line("  const double inv%d = 1.0 / %s;", opi, A(0).c_str());
-                } else {
-                    Terms t;
-                    for (int i = 0; i <= k - 1; i++) {
-                        /* rr = pw*(k-i) - i, evaluated with the oracle's two IEEE operations */
-                        volatile double m = pw * (double)(k - i);
-                        volatile double rr = m - (double)i;
-                        if (fast) {
-                            std::string w = fmt("w%d", tmpc++);
-                            e.line("  const double %s = %s * %s;", w.c_str(), dlit(rr).c_str(), C(i).c_str());
-                            term(t, w, A(k - i));
-                        } else term(t, fmt("M_(%s, %s)", dlit(rr).c_str(), C(i).c_str()), A(k - i));
-                    }
-                    std::string s = sum(e, t);
-                    if (fast) e.line("  const double %s = %s * (inv%d * %s);", r, s.c_str(), opi, dlit(1.0 / k).c_str());
-                    else e.line("  const double %s = D_(%s, M_(%s, %s));", r, s.c_str(), dlit((double)k).c_str(), A(0).c_str());
-                }
+            }
+            case TB_OP_POW: {
+                std::string a = A(0);
+                e.line("  const double %s = tb_pow(%s, %s);", r, a.c_str(), dlit(pw).c_str());
+                if (fast) e.line("  const double inv%d = 1.0 / %s;", opi, a.c_str());
                 break;
-            case TB_OP_EXP:
-                if (k0) e.line("  const double %s = tb_exp(%s);", r, A(0).c_str());
-                else {
-                    Terms t;
-                    for (int i = 0; i <= k - 1; i++) {
-                        if (fast) {
-                            std::string w = fmt("w%d", tmpc++);
-                            e.line("  const double %s = %s * %s;", w.c_str(), dlit((double)(k - i)).c_str(), A(k - i).c_str());
-                            term(t, w, C(i));
-                        } else term(t, fmt("M_(%s, %s)", dlit((double)(k - i)).c_str(), A(k - i).c_str()), C(i));
-                    }
-                    std::string s = sum(e, t);
-                    if (fast) e.line("  const double %s = %s * %s;", r, s.c_str(), dlit(1.0 / k).c_str());
-                    else e.line("  const double %s = %s;", r, divc(s, k).c_str());
-                }
-                break;
+            }
+            case TB_OP_EXP: { std::string a = A(0); e.line("  const double %s = tb_exp(%s);", r, a.c_str()); break; }
             case TB_OP_LOG:
-                if (k0) { e.line("  const double %s = tb_log(%s);", r, A(0).c_str()); if (fast) e.line("  const double inv%d = 1.0 / %s;", opi, A(0).c_str()); }
-                else if (k == 1) {
-                    if (fast) e.line("  const double %s = %s * inv%d;", r, A(1).c_str(), opi);
-                    else e.line("  const double %s = D_(%s, %s);", r, A(1).c_str(), A(0).c_str());
-                } else {
-                    Terms t;
-                    term(t, fmt("M_(%s, %s)", dlit((double)(k - 1)).c_str(), A(1).c_str()), C(k - 1));
-                    for (int i = 2; i <= k - 1; i++) term(t, fmt("M_(%s, %s)", dlit((double)(k - i)).c_str(), A(i).c_str()), C(k - i));
-                    std::string s = sum(e, t);
-                    if (fast) e.line("  const double %s = fma(-%s, %s, %s) * inv%d;", r, s.c_str(), dlit(1.0 / k).c_str(), A(k).c_str(), opi);
-                    else e.line("  const double %s = D_(B_(%s, %s), %s);", r, A(k).c_str(), divc(s, k).c_str(), A(0).c_str());
+                if (k0) {
+                    std::string a = A(0);
+                    e.line("  const double %s = tb_log(%s);", r, a.c_str());
+                    if (fast) e.line("  const double inv%d = 1.0 / %s;", opi, a.c_str());
+                } else { /* k == 1 */
+                    std::string a1 = A(1), a0 = A(0);
+                    if (fast) e.line("  const double %s = %s * inv%d;", r, a1.c_str(), opi);
+                    else e.line("  const double %s = D_(%s, %s);", r, a1.c_str(), a0.c_str());
                 }
                 break;
             case TB_OP_SINCOS: {
                 const std::string RC = vname(op.aux, k);
-                auto Cc = [&](int idx) { return rd(op.aux, idx, k, defined); };
-                if (k0) e.line("  double %s, %s; tb_sincos(%s, &%s, &%s);", r, RC.c_str(), A(0).c_str(), r, RC.c_str());
-                else {
-                    Terms ts, tc;
-                    for (int i = 1; i <= k; i++) {
-                        std::string x = A(i);
-                        if (fast && x == "0.0") continue;
-                        if (i >= 2) {
-                            std::string w = fmt("w%d", tmpc++);
-                            e.line("  const double %s = M_(%s, %s);", w.c_str(), dlit((double)i).c_str(), x.c_str());
-                            x = w;
-                        }
-                        ts.push_back({x, Cc(k - i)});
-                        tc.push_back({x, C(k - i)});
-                    }
-                    std::string s1 = sum(e, ts), s2 = sum(e, tc, true);
-                    if (fast) {
-                        e.line("  const double %s = %s * %s;", r, s1.c_str(), dlit(1.0 / k).c_str());
-                        e.line("  const double %s = %s * %s;", RC.c_str(), s2.c_str(), dlit(1.0 / k).c_str());
-                    } else {
-                        e.line("  const double %s = %s;", r, divc(s1, k).c_str());
-                        e.line("  const double %s = %s;", RC.c_str(), divc(s2, k).c_str());
-                    }
-                }
-                store(e, op.aux, k, RC);
-                defined.insert(op.aux);
+                std::string a = A(0);
+                e.line("  double %s, %s; tb_sincos(%s, &%s, &%s);", r, RC.c_str(), a.c_str(), r, RC.c_str());
+                define(e, op.aux, k, RC);
                 break;
             }
             default: err = "opcode not supported by the unrolled code generator"; break;
         }
-        store(e, op.res, k, R);
-        defined.insert(op.res);
+        define(e, op.res, k, R);
     }
 
+    /* ---- recurrence sums --------------------------------------------------------
+     * A chain is one left-to-right sum of products (coef*u)*v.  Parity mode emits
+     * acc = acc + (coef*u)*v with unfused operations in the oracle's order; fast
+     * mode uses FMA and `nacc` partial accumulators.  The chains of a group are
+     * emitted round-robin, one term each, so that (a) the two orders of a pair
+     * share every loaded coefficient and (b) independent add chains interleave.  */
+    struct Term { bool has_coef; double coef; Ref u, v; };
+    struct Chain {
+        std::vector<Term> terms;
+        bool neg = false;
+        size_t pos = 0;
+        std::string acc;
+        int nacc = 1;
+    };
+    struct SNode {
+        int j = 0, k = 0;
+        std::vector<Chain> ch;
+        bool fin = false;
+    };
+
+    void push_term(Chain &c, const Ref &u, const Ref &v, bool has_coef = false, double coef = 0.0) {
+        auto tz = [&](const Ref &r) { return TB_OPERAND_KIND(r.o) == TB_K_TIME && r.idx >= 2; };
+        if (fast && (tz(u) || tz(v))) return; /* structural zeros of the time series */
+        c.terms.push_back({has_coef, coef, u, v});
+    }
+    void build_chains(SNode &n) {
+        const tb_op_t &op = ode.ops[n.j];
+        const int k = n.k;
+        n.ch.assign(1, Chain());
+        Chain &c = n.ch[0];
+        switch (eff_op(op)) {
+            case TB_OP_MUL: for (int i = 0; i <= k; i++) push_term(c, {op.a, i}, {op.b, k - i}); break;
+            case TB_OP_SQR: { const int kodd = k & 1, kend = (k - 2 + kodd) / 2; for (int i = 0; i <= kend; i++) push_term(c, {op.a, i}, {op.a, k - i}); break; }
+            case TB_OP_DIV: for (int i = 0; i <= k - 1; i++) push_term(c, {op.res, i}, {op.b, k - i}); break;
+            case TB_OP_SQRT: { const int kodd = k & 1, kend = (k - 2 + kodd) / 2; for (int i = 1; i <= kend; i++) push_term(c, {op.res, i}, {op.res, k - i}); break; }
+            case TB_OP_POW:
+                for (int i = 0; i <= k - 1; i++) { /* rr = pw*(k-i) - i with the oracle's two IEEE operations */
+                    volatile double m = op.imm * (double)(k - i);
+                    volatile double rr = m - (double)i;
+                    push_term(c, {op.res, i}, {op.a, k - i}, true, rr);
+                }
+                break;
+            case TB_OP_EXP: for (int i = 0; i <= k - 1; i++) push_term(c, {op.a, k - i}, {op.res, i}, true, (double)(k - i)); break;
+            case TB_OP_LOG:
+                push_term(c, {op.a, 1}, {op.res, k - 1}, true, (double)(k - 1));
+                for (int i = 2; i <= k - 1; i++) push_term(c, {op.a, i}, {op.res, k - i}, true, (double)(k - i));
+                break;
+            case TB_OP_SINCOS: {
+                n.ch.push_back(Chain());
+                Chain &s = n.ch[0], &cc = n.ch[1];
+                cc.neg = true;
+                for (int i = 1; i <= k; i++) {
+                    push_term(s, {op.a, i}, {op.aux, k - i}, i >= 2, (double)i);
+                    push_term(cc, {op.a, i}, {op.res, k - i}, i >= 2, (double)i);
+                }
+                break;
+            }
+            default: break;
+        }
+    }
+    /* coef*u, computed once per group (the two chains of sincos! share it) */
+    std::string scaled_val(Em &e, const Term &t) {
+        std::string u = val(e, t.u);
+        if (!t.has_coef) return u;
+        std::string c = dlit(t.coef);
+        auto key = std::make_pair(c, u);
+        auto it = scaled.find(key);
+        if (it != scaled.end()) return it->second;
+        std::string w = fmt("w%d", tmpc++);
+        e.line("  const double %s = M_(%s, %s);", w.c_str(), c.c_str(), u.c_str());
+        scaled[key] = w;
+        return w;
+    }
+    void emit_term(Em &e, Chain &c, const Term &t) {
+        std::string x = scaled_val(e, t), y = val(e, t.v);
+        const size_t i = c.pos;
+        if (c.acc.empty()) c.acc = fmt("a%d", tmpc++);
+        const char *a = c.acc.c_str();
+        if (!fast) {
+            if (i == 0) e.line("  double %s = M_(%s%s%s, %s);", a, c.neg ? "N_(" : "", x.c_str(), c.neg ? ")" : "", y.c_str());
+            else e.line("  %s = %s(%s, M_(%s, %s));", a, c.neg ? "B_" : "A_", a, x.c_str(), y.c_str());
+        } else {
+            const int j = (int)(i % (size_t)c.nacc);
+            if (i < (size_t)c.nacc) e.line("  double %s_%d = %s * %s;", a, j, x.c_str(), y.c_str());
+            else e.line("  %s_%d = fma(%s, %s, %s_%d);", a, j, x.c_str(), y.c_str(), a, j);
+        }
+    }
+    /* name (or literal) holding the finished sum */
+    std::string chain_sum(Em &e, Chain &c) {
+        if (c.terms.empty()) return "0.0";
+        if (!fast) return c.acc;
+        const int n = (int)std::min<size_t>((size_t)c.nacc, c.terms.size());
+        const char *a = c.acc.c_str();
+        std::string comb;
+        if (n == 1) comb = fmt("%s_0", a);
+        else if (n == 2) comb = fmt("%s_0 + %s_1", a, a);
+        else if (n == 3) comb = fmt("(%s_0 + %s_1) + %s_2", a, a, a);
+        else comb = fmt("(%s_0 + %s_1) + (%s_2 + %s_3)", a, a, a, a);
+        std::string s = fmt("s%d", tmpc++);
+        e.line("  const double %s = %s(%s);", s.c_str(), c.neg ? "-" : "", comb.c_str());
+        return s;
+    }
+    bool fin_ready(const SNode &n) const {
+        const tb_op_t &op = ode.ops[n.j];
+        const int k = n.k, o = eff_op(op);
+        if ((o == TB_OP_DIV && !u_is_num(op.a)) || o == TB_OP_SQRT || o == TB_OP_LOG) if (!avail({op.a, k})) return false;
+        if (o == TB_OP_SQR && !(k & 1) && !avail({op.a, k / 2})) return false;
+        if (o == TB_OP_SQRT && !(k & 1) && !avail({op.res, (k - 2) / 2 + 1})) return false;
+        return true;
+    }
+    void finalize(Em &e, SNode &n) {
+        const tb_op_t &op = ode.ops[n.j];
+        const int k = n.k, opi = n.j, o = eff_op(op);
+        const bool sa = u_is_num(op.a);
+        const std::string R = vname(op.res, k);
+        const char *r = R.c_str();
+        std::string s = chain_sum(e, n.ch[0]);
+        auto A = [&](int idx) { return val(e, {op.a, idx}); };
+        switch (o) {
+            case TB_OP_MUL: e.line("  const double %s = %s;", r, s.c_str()); break;
+            case TB_OP_SQR:
+                if (k & 1) e.line("  const double %s = M_(2.0, %s);", r, s.c_str());
+                else {
+                    std::string h = A(k / 2);
+                    if (fast) e.line("  const double %s = fma(%s, %s, 2.0 * %s);", r, h.c_str(), h.c_str(), s.c_str());
+                    else e.line("  const double %s = A_(M_(2.0, %s), M_(%s, %s));", r, s.c_str(), h.c_str(), h.c_str());
+                }
+                break;
+            case TB_OP_DIV:
+                if (fast) {
+                    if (sa) e.line("  const double %s = -%s * inv%d;", r, s.c_str(), opi);
+                    else { std::string a = A(k); e.line("  const double %s = (%s - %s) * inv%d;", r, a.c_str(), s.c_str(), opi); }
+                } else {
+                    if (sa) e.line("  const double %s = DIVY_(N_(%s), den%d, inv%d, ok%d);", r, s.c_str(), opi, opi, opi);
+                    else { std::string a = A(k); e.line("  const double %s = DIVY_(B_(%s, %s), den%d, inv%d, ok%d);", r, a.c_str(), s.c_str(), opi, opi, opi); }
+                }
+                break;
+            case TB_OP_SQRT: {
+                std::string a = A(k);
+                const bool even = !(k & 1);
+                std::string c = even ? val(e, {op.res, (k - 2) / 2 + 1}) : std::string();
+                if (fast) {
+                    if (!even) e.line("  const double %s = fma(-2.0, %s, %s) * inv%d;", r, s.c_str(), a.c_str(), opi);
+                    else e.line("  const double %s = fma(-%s, %s, fma(-2.0, %s, %s)) * inv%d;", r, c.c_str(), c.c_str(), s.c_str(), a.c_str(), opi);
+                } else {
+                    std::string aux = fmt("B_(%s, M_(2.0, %s))", a.c_str(), s.c_str());
+                    if (even) aux = fmt("B_(%s, M_(%s, %s))", aux.c_str(), c.c_str(), c.c_str());
+                    e.line("  const double %s = DIVY_(%s, den%d, inv%d, ok%d);", r, aux.c_str(), opi, opi, opi);
+                }
+                break;
+            }
+            case TB_OP_POW:
+                if (fast) e.line("  const double %s = %s * (inv%d * %s);", r, s.c_str(), opi, dlit(1.0 / k).c_str());
+                else { std::string a0 = A(0); e.line("  const double %s = DIVQ_(%s, M_(%s, %s));", r, s.c_str(), dlit((double)k).c_str(), a0.c_str()); }
+                break;
+            case TB_OP_EXP:
+                if (fast) e.line("  const double %s = %s * %s;", r, s.c_str(), dlit(1.0 / k).c_str());
+                else e.line("  const double %s = %s;", r, divc(s, k).c_str());
+                break;
+            case TB_OP_LOG: {
+                std::string a = A(k);
+                if (fast) e.line("  const double %s = fma(-%s, %s, %s) * inv%d;", r, s.c_str(), dlit(1.0 / k).c_str(), a.c_str(), opi);
+                else { std::string a0 = A(0); e.line("  const double %s = DIVQ_(B_(%s, %s), %s);", r, a.c_str(), divc(s, k).c_str(), a0.c_str()); }
+                break;
+            }
+            case TB_OP_SINCOS: {
+                const std::string RC = vname(op.aux, k);
+                std::string s2 = chain_sum(e, n.ch[1]);
+                if (fast) {
+                    e.line("  const double %s = %s * %s;", r, s.c_str(), dlit(1.0 / k).c_str());
+                    e.line("  const double %s = %s * %s;", RC.c_str(), s2.c_str(), dlit(1.0 / k).c_str());
+                } else {
+                    e.line("  const double %s = %s;", r, divc(s, k).c_str());
+                    e.line("  const double %s = %s;", RC.c_str(), divc(s2, k).c_str());
+                }
+                define(e, op.aux, k, RC);
+                break;
+            }
+            default: err = "internal: not a sum entry"; break;
+        }
+        define(e, op.res, k, R);
+        n.fin = true;
+    }
+
+    /* emit a group of sum nodes, chains interleaved one term per sweep */
+    void emit_group(Em &e, std::vector<SNode> &g) {
+        loaded.clear();
+        scaled.clear();
+        size_t nchains = 0;
+        for (SNode &n : g) { build_chains(n); nchains += n.ch.size(); }
+        for (SNode &n : g)
+            for (Chain &c : n.ch) c.nacc = fast ? (nchains >= 4 ? 2 : 4) : 1;
+        bool progress = true;
+        while (progress) {
+            progress = false;
+            for (SNode &n : g) {
+                if (n.fin) continue;
+                bool all = true;
+                for (Chain &c : n.ch) {
+                    if (c.pos < c.terms.size()) {
+                        const Term &t = c.terms[c.pos];
+                        if (avail(t.u) && avail(t.v)) { emit_term(e, c, t); c.pos++; progress = true; }
+                    }
+                    if (c.pos < c.terms.size()) all = false;
+                }
+                if (all && fin_ready(n)) { finalize(e, n); progress = true; }
+            }
+        }
+        for (SNode &n : g) if (!n.fin && err.empty()) err = "internal: recurrence group did not complete";
+    }
     /* parity-mode x / n for a small integer constant n: exact multiply for powers of two,
      * Markstein correction (tb_div_y) otherwise -- same bits as the IEEE division      */
     std::string divc(const std::string &x, int n) {
         if ((n & (n - 1)) == 0) return fmt("M_(%s, %s)", x.c_str(), dlit(1.0 / n).c_str());
-        return fmt("tb_div_y(%s, %s, %s, true)", x.c_str(), dlit((double)n).c_str(), dlit(1.0 / n).c_str());
+        return fmt("DIVY_(%s, %s, %s, true)", x.c_str(), dlit((double)n).c_str(), dlit(1.0 / n).c_str());
     }
 
     void store(Em &e, int32_t o, int k, const std::string &v) {
@@ -401,30 +554,112 @@ struct UGen {
         else if (it->second.place == PL_SMEM) e.line("  S(%d, %d) = %s;", it->second.id, k, v.c_str());
     }
 
-    /* jetcoeffs!: all orders, straight line */
+
+    /* jetcoeffs!: dataflow-scheduled straight-line code.  Entries whose inputs are
+     * known are emitted as early as possible; ready recurrence entries of the lowest
+     * order form a group, and each takes its next order along as a PAIR when that
+     * one only waits for the first's own result (x'' = f systems such as Kepler and
+     * the pendulum: x[k+2] follows from order k).  Every value is computed by the
+     * same expression as in order-by-order emission, so parity mode stays bitwise. */
     void emit_jets(Em &e) {
         const tb_ode_desc_t &d = ode.desc;
-        e.line("__device__ __forceinline__ void tb_u_jets(TbJets &J, double *__restrict__ smt, const double *__restrict__ par,");
-        e.line("                                          const double t0, const double *__restrict__ x0) {");
+        const bool pairing = !(co.flags & 16), grouping = !(co.flags & 32);
+        Em &out = e;
+        Em body;
+        {
+        Em &e = body;
         for (int c = 0; c < d.dof; c++) {
             e.line("  const double vX%d_0 = x0[%d];", c, c);
-            store(e, TB_OPERAND(TB_K_X, c), 0, fmt("vX%d_0", c));
+            define(e, TB_OPERAND(TB_K_X, c), 0, fmt("vX%d_0", c));
         }
-        for (int k = 0; k < P; k++) {
-            e.line("  /* ---- order %d ---- */", k);
-            if (k > 0 && !(co.flags & 8)) e.line("  asm volatile(\"\" ::: \"memory\");");
-            std::set<int32_t> defined;
-            for (int j = 0; j < d.nops; j++) emit_op(e, j, ode.ops[j], k, defined);
-            for (int c = 0; c < d.dof; c++) { /* solcoeff!: x[k+1] = dx[k]/(k+1) */
-                int32_t dx = TB_OPERAND(TB_K_DX, c);
-                if (!defined.count(dx)) { err = "tape does not define dx[" + std::to_string(c) + "]"; return; }
-                std::string v = fmt("vX%d_%d", c, k + 1);
-                if (fast) e.line("  const double %s = %s * %s;", v.c_str(), vname(dx, k).c_str(), dlit(1.0 / (k + 1)).c_str());
-                else e.line("  const double %s = %s;", v.c_str(), divc(vname(dx, k), k + 1).c_str());
-                store(e, TB_OPERAND(TB_K_X, c), k + 1, v);
+        std::vector<std::vector<char>> done(d.nops, std::vector<char>(P, 0));
+        std::vector<std::vector<char>> xdone(d.dof, std::vector<char>(P + 1, 0));
+        long remaining = (long)d.nops * P + (long)d.dof * P;
+        auto update_cur = [&]() {
+            int c = P;
+            for (int j = 0; j < d.nops; j++)
+                for (int k = 0; k < P; k++) if (!done[j][k]) { c = std::min(c, k); break; }
+            cur = c;
+        };
+        while (remaining > 0 && err.empty()) {
+            bool progress = true, any = false;
+            while (progress) { /* entries without sums, and solcoeff!, to a fixed point */
+                progress = false;
+                for (int k = 0; k < P; k++) {
+                    for (int j = 0; j < d.nops; j++) {
+                        const tb_op_t &op = ode.ops[j];
+                        if (done[j][k] || is_sum_node(op, k) || !node_ready(op, k)) continue;
+                        emit_cheap(e, j, op, k);
+                        done[j][k] = 1; remaining--; progress = any = true;
+                    }
+                    for (int c = 0; c < d.dof; c++) { /* solcoeff!: x[k+1] = dx[k]/(k+1) */
+                        const int32_t dx = TB_OPERAND(TB_K_DX, c);
+                        if (xdone[c][k + 1] || !computed.count(Key(dx, k))) continue;
+                        std::string v = fmt("vX%d_%d", c, k + 1);
+                        if (fast) e.line("  const double %s = %s * %s;", v.c_str(), vname(dx, k).c_str(), dlit(1.0 / (k + 1)).c_str());
+                        else e.line("  const double %s = %s;", v.c_str(), divc(vname(dx, k), k + 1).c_str());
+                        define(e, TB_OPERAND(TB_K_X, c), k + 1, v);
+                        xdone[c][k + 1] = 1; remaining--; progress = any = true;
+                    }
+                }
             }
+            update_cur();
+            std::vector<SNode> g;
+            int kmin = -1;
+            for (int k = 1; k < P && kmin < 0; k++)
+                for (int j = 0; j < d.nops; j++)
+                    if (!done[j][k] && is_sum_node(ode.ops[j], k) && node_ready(ode.ops[j], k)) { kmin = k; break; }
+            if (kmin >= 0) {
+                for (int j = 0; j < d.nops; j++) {
+                    const tb_op_t &op = ode.ops[j];
+                    if (done[j][kmin] || !is_sum_node(op, kmin) || !node_ready(op, kmin)) continue;
+                    SNode n; n.j = j; n.k = kmin;
+                    g.push_back(n);
+                    done[j][kmin] = 1; remaining--;
+                    if (pairing && kmin + 1 < P && !done[j][kmin + 1] && is_sum_node(op, kmin + 1) && node_ready(op, kmin + 1, kmin)) {
+                        SNode m; m.j = j; m.k = kmin + 1;
+                        g.push_back(m);
+                        done[j][kmin + 1] = 1; remaining--;
+                    }
+                    if (!grouping) break;
+                }
+                e.line("  /* ---- order %d: %d recurrence chain group ---- */", kmin, (int)g.size());
+                emit_group(e, g);
+                if (!(co.flags & 8)) e.line("  asm volatile(\"\" ::: \"memory\");");
+                any = true;
+            }
+            if (!any) { err = "tape has a dependency cycle or an undefined operand (dx not defined?)"; break; }
         }
-        e.line("}");
+        }
+        const char *sig = "(TbJets &J, double *__restrict__ smt, const double *__restrict__ par, const double t0, const double *__restrict__ x0)";
+        const bool quick = !fast && !(co.flags & 64);
+        if (quick) {
+            /* parity mode, two copies of the body: the QUICK one divides with unguarded Markstein /
+             * Newton sequences and folds every operand's exponent into one running maximum; when
+             * that leaves the proven range (zero, subnormal-ish, huge, Inf, NaN operands) the step
+             * is recomputed by the SAFE copy with IEEE divisions.  Same bits either way; the quick
+             * copy is branch-free, so ptxas schedules each order as one basic block.             */
+            out.line("#define DIVY_(a, b, y, ok) tb_divy_q((a), (b), (y), chk)");
+            out.line("#define DIVQ_(a, b) tb_div_q((a), (b), chk)");
+            out.line("#define DENCHK_(d) chk = max(chk, tb_rng(d))");
+            out.line("__device__ __forceinline__ unsigned tb_u_jets_q%s {", sig);
+            out.line("  unsigned chk = 0u;");
+            out.s += body.s;
+            out.line("  return chk;");
+            out.line("}");
+            out.line("#undef DIVY_\n#undef DIVQ_\n#undef DENCHK_");
+        }
+        out.line("#define DIVY_(a, b, y, ok) tb_div_y((a), (b), (y), (ok))");
+        out.line("#define DIVQ_(a, b) D_((a), (b))");
+        out.line("#define DENCHK_(d)");
+        out.line("__device__ __forceinline__ void tb_u_jets%s%s {", quick ? "_s" : "", sig);
+        out.s += body.s;
+        out.line("}");
+        if (quick) {
+            out.line("__device__ __forceinline__ void tb_u_jets%s {", sig);
+            out.line("  if (tb_u_jets_q(J, smt, par, t0, x0) >= TB_RNG_SPAN) tb_u_jets_s(J, smt, par, t0, x0);");
+            out.line("}");
+        }
     }
 
     /* coefficient k of state jet c; resolves to a register, an LDS or a scaled dx
