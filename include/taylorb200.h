@@ -182,6 +182,12 @@ typedef struct tb_compile_opts {
 #define TB_CF_NO_DISK_CACHE 1 /* do not read/write the on-disk cubin cache    */
 #define TB_CF_KEEP_SOURCE 2   /* (always on) keep generated source for tb_get_source */
 #define TB_CF_ROLLED 4        /* force kernel variant 1 (rolled loops, all jets in shared memory) */
+/* tuning switches of the unrolled generator (variant 2); all default off */
+#define TB_CF_NO_MEMBAR 8     /* no compiler memory barrier between recurrence groups */
+#define TB_CF_NO_PAIRING 16   /* do not emit two consecutive orders of a recurrence together */
+#define TB_CF_NO_GROUPING 32  /* one recurrence entry per group (no interleaving of independent sums) */
+#define TB_CF_NO_QUICK 64     /* parity mode: single jet body with guarded divisions */
+#define TB_CF_BLOCK_LOCKSTEP 128 /* barrier per order: the warps of a block share one instruction stream */
 
 /* ---- integration options: keyword arguments of taylorinteg -------------- */
 typedef struct tb_opts {

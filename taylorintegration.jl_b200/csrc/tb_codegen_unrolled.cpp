@@ -581,6 +581,7 @@ struct UGen {
                 for (int k = 0; k < P; k++) if (!done[j][k]) { c = std::min(c, k); break; }
             cur = c;
         };
+        int last_sync_k = -1;
         while (remaining > 0 && err.empty()) {
             bool progress = true, any = false;
             while (progress) { /* entries without sums, and solcoeff!, to a fixed point */
@@ -623,6 +624,7 @@ struct UGen {
                     }
                     if (!grouping) break;
                 }
+                if ((co.flags & 128) && kmin != last_sync_k) { e.line("  TB_ORDER_SYNC();"); last_sync_k = kmin; }
                 e.line("  /* ---- order %d: %d recurrence chain group ---- */", kmin, (int)g.size());
                 emit_group(e, g);
                 if (!(co.flags & 8)) e.line("  asm volatile(\"\" ::: \"memory\");");
@@ -642,16 +644,18 @@ struct UGen {
             out.line("#define DIVY_(a, b, y, ok) tb_divy_q((a), (b), (y), chk)");
             out.line("#define DIVQ_(a, b) tb_div_q((a), (b), chk)");
             out.line("#define DENCHK_(d) chk = max(chk, tb_rng(d))");
+            out.line("#define TB_ORDER_SYNC() %s", (co.flags & 128) ? "__syncthreads()" : "");
             out.line("__device__ __forceinline__ unsigned tb_u_jets_q%s {", sig);
             out.line("  unsigned chk = 0u;");
             out.s += body.s;
             out.line("  return chk;");
             out.line("}");
-            out.line("#undef DIVY_\n#undef DIVQ_\n#undef DENCHK_");
+            out.line("#undef DIVY_\n#undef DIVQ_\n#undef DENCHK_\n#undef TB_ORDER_SYNC");
         }
         out.line("#define DIVY_(a, b, y, ok) tb_div_y((a), (b), (y), (ok))");
         out.line("#define DIVQ_(a, b) D_((a), (b))");
         out.line("#define DENCHK_(d)");
+        out.line("#define TB_ORDER_SYNC() %s", (!quick && (co.flags & 128)) ? "__syncthreads()" : "");
         out.line("__device__ __forceinline__ void tb_u_jets%s%s {", quick ? "_s" : "", sig);
         out.s += body.s;
         out.line("}");
@@ -737,6 +741,7 @@ int generate_unrolled(const Ode &ode, const tb_compile_opts_t &co, Layout &L, st
     e.line("#define TB_KIND %d", co.kind);
     e.line("#define TB_EV_NOPS 0");
     e.line("#define TB_JAC_NOPS 0");
+    e.line("#define TB_BAR %d", (co.flags & 128) ? 1 : 0);
     e.s += embedded_math_h();
     e.s += embedded_device_pre();
     e.line("/* placement: %d series in registers, %d in shared memory */", g.nreg, g.nsm);

@@ -16,6 +16,9 @@
 #ifndef TB_VARIANT
 #define TB_VARIANT 1
 #endif
+#ifndef TB_BAR
+#define TB_BAR 0
+#endif
 
 /* _stepsize: src/integrator/stepsize.jl:107-111   (eps/a)^(1/k).  Not inlined: the
  * double-double pow is ~300 instructions and is called 2*dof times per step.    */
@@ -139,6 +142,29 @@ __device__ __forceinline__ double tb_u_stepsize(const TbJets &J, const double *_
         if (m1 != 0.0) l = fmin(l, (le - log(m1)) * (1.0 / (double)(TB_P - 1)));
         if (m2 != 0.0) l = fmin(l, (le - log(m2)) * (1.0 / (double)TB_P));
         if (l != TB_INF) h = exp(l);
+    } else
+#else
+    if (a.reltol == 0.0) {
+        /* Parity mode, reltol == 0: min_c pow(eps/|x_c[k]|, 1/k) is attained at the largest
+         * |x_c[k]| (IEEE division is monotone; tb_pow errs by < 1 ulp, so two arguments that
+         * differ by more than 2^-40 relative cannot swap order after the 1/k-th power).  Only
+         * components within 2^-40 of the maximum are evaluated as well: same bits as the
+         * reference's loop over all components (stepsize.jl:83-86), 2 pow calls instead of 2*dof.
+         * NaN coefficients drop out of fmax here exactly as they drop out of min there.       */
+#pragma unroll
+        for (int k = TB_P - 1; k <= TB_P; k++) {
+            double m = 0.0, ac[TB_DOF];
+#pragma unroll
+            for (int c = 0; c < TB_DOF; c++) { ac[c] = fabs(TB_X(c, k)); m = fmax(m, ac[c]); }
+            if (m != 0.0) {
+                double hk = tb_stepsize_k(m, a.abstol, k);
+                const double thr = M_(m, 0.99999999999909051);
+#pragma unroll
+                for (int c = 0; c < TB_DOF; c++)
+                    if (ac[c] != m && ac[c] > thr) hk = fmin(hk, tb_stepsize_k(ac[c], a.abstol, k));
+                h = fmin(h, hk);
+            }
+        }
     } else
 #endif
     {
@@ -371,11 +397,12 @@ __device__ __forceinline__ void tb_store_psol(const TbTraj &T, TB_JETS_PARAMS, c
 }
 
 /* One iteration of the driver loop; returns true when the trajectory is done. */
-__device__ __forceinline__ bool tb_traj_step(TbTraj &T, double *__restrict__ smt, const TbArgs &a) {
+__device__ __forceinline__ bool tb_traj_step(TbTraj &T, double *__restrict__ smt, const TbArgs &a, const bool live) {
 #if TB_KIND == 0
     /* taylorinteg!: src/integrator/taylorinteg.jl:356-378 (t0,tmax) and 607-639 (trange) */
     TB_JETS_DECL
-    TB_COMPUTE_JETS(T);
+    TB_COMPUTE_JETS(T); /* block-lockstep build (TB_BAR): idle lanes run the jets too, for the barriers inside */
+    if (!live) return false;
     double dt = TB_STEPSIZE(a);
     if (dt == 0.0) { T.st |= TB_ST_ZERO_STEP; return true; }
     const double rem = B_(T.tmax, T.t0);
@@ -538,32 +565,49 @@ extern "C" __global__ void __launch_bounds__(TB_BT, TB_MINB) tb_ensemble_kernel(
     const unsigned full = 0xffffffffu;
     const int lane = threadIdx.x & 31;
     TbTraj T;
-    bool have = false;
+#if TB_BAR
+    /* idle lanes execute the jet code on whatever T holds: give it defined numbers */
+#pragma unroll
+    for (int c = 0; c < TB_NX; c++) T.x0[c] = 1.0;
+#pragma unroll
+    for (int j = 0; j < (TB_NPAR > 0 ? TB_NPAR : 1); j++) T.par[j] = 1.0;
+    T.t0 = 0.0;
+#endif
+    bool have = false, more = true;
     for (;;) {
         if (a.lockstep) {
-            if (!__any_sync(full, have)) {
+            if (more && !__any_sync(full, have)) {
                 unsigned long long base = 0;
                 if (lane == 0) base = atomicAdd(a.counter, 32ull);
                 base = __shfl_sync(full, base, 0);
-                if (base >= (unsigned long long)a.N) break;
-                long long i = (long long)base + lane;
-                if (i < a.N) {
-                    have = true;
-                    if (tb_traj_init(T, smt, a, i)) { tb_traj_finish(T, a); have = false; }
+                if (base >= (unsigned long long)a.N) more = false;
+                else {
+                    long long i = (long long)base + lane;
+                    if (i < a.N) {
+                        have = true;
+                        if (tb_traj_init(T, smt, a, i)) { tb_traj_finish(T, a); have = false; }
+                    }
                 }
             }
         } else {
-            while (!have) {
+            while (!have && more) {
                 long long i = (long long)atomicAdd(a.counter, 1ull);
-                if (i >= a.N) break;
+                if (i >= a.N) { more = false; break; }
                 have = true;
                 if (tb_traj_init(T, smt, a, i)) { tb_traj_finish(T, a); have = false; }
             }
-            if (!__any_sync(full, have)) break;
         }
+#if TB_BAR
+        /* block lockstep: every warp runs every step until the whole block is out of work, so the
+         * barriers inside the jet code are uniform and the warps share one instruction stream  */
+        if (!__syncthreads_or(have || (a.lockstep && more))) break;
+        if (tb_traj_step(T, smt, a, have)) { tb_traj_finish(T, a); have = false; }
+#else
+        if (!__any_sync(full, have)) { if (!(a.lockstep && more)) break; else continue; }
         if (have) {
-            if (tb_traj_step(T, smt, a)) { tb_traj_finish(T, a); have = false; }
+            if (tb_traj_step(T, smt, a, true)) { tb_traj_finish(T, a); have = false; }
         }
+#endif
     }
 }
 
