@@ -113,12 +113,14 @@ struct UGen {
                 default: break;
             }
         }
-        /* state jets: stored unless derivable from a stored dx (fast mode only) */
+        /* state jets: stored unless no recurrence reads them and dx is stored: then x[k] = dx[k-1]/k is
+         * recomputed where Horner / stepsize need it (same expression, same bits), which frees
+         * shared memory for more resident trajectories                                           */
         for (int c = 0; c < d.dof; c++) {
             int32_t x = TB_OPERAND(TB_K_X, c), dx = TB_OPERAND(TB_K_DX, c);
             bool cauchy = ser.count(x) && ser[x].reads > 0;
             bool dx_stored = ser.count(dx) && ser[dx].reads > 0;
-            if (!cauchy && fast && dx_stored) { ser[x].place = PL_DERIVED; ser[x].id = c; }
+            if (!cauchy && dx_stored && !(co.flags & 256)) { ser[x].place = PL_DERIVED; ser[x].id = c; }
             else ser[x].reads += 0.0; /* creates the entry: stored */
         }
         /* placement by read count */
@@ -679,7 +681,8 @@ struct UGen {
             else {
                 const SeriesInfo &di = ser[TB_OPERAND(TB_K_DX, c)];
                 std::string ref = di.place == PL_REG ? fmt("J.r%d[k - 1]", di.id) : fmt("S(%d, k - 1)", di.id);
-                e.line("    case %d: return k == 0 ? x0[%d] : %s * (1.0 / (double)k);", c, c, ref.c_str());
+                if (fast) e.line("    case %d: return k == 0 ? x0[%d] : %s * (1.0 / (double)k);", c, c, ref.c_str());
+                else e.line("    case %d: return k == 0 ? x0[%d] : tb_divc(%s, k);", c, c, ref.c_str());
             }
         }
         e.line("    default: return 0.0;");
