@@ -44,6 +44,7 @@ def parse_args():
     ap.add_argument("--cpu-seconds", type=float, default=15.0, help="target CPU time of the cpu_baseline sample")
     ap.add_argument("--no-cpu-baseline", action="store_true")
     ap.add_argument("--no-e2e", action="store_true")
+    ap.add_argument("--no-fast", action="store_true", help="skip the extra fast-mode (FMA) measurement")
     ap.add_argument("--reg-budget", type=int, default=0, help="doubles of jet storage in registers (kernel variant 2)")
     ap.add_argument("--block-threads", type=int, default=0)
     ap.add_argument("--kflags", type=int, default=0, help="TB_CF_* compile flags (4 = rolled variant 1)")
@@ -209,6 +210,13 @@ def run_b200(a):
         if world > 1:  # the path's only exchange: final gather of the shards' results
             dist.all_gather_into_tensor(gathered, d_xf)
 
+    kcur = [k]
+
+    def step_device_k():
+        L.check(lib.tb_integrate_device(kcur[0].handle, N, d_q0.data_ptr(), d_mu.data_ptr(), w["t0"], w["tmax"], None, 0,
+                                        C.byref(opts), C.byref(d_out), d_work.data_ptr(), stream.cuda_stream),
+                "tb_integrate_device")
+
     def step_host():
         L.check(lib.tb_integrate(k.handle, N, h_q0.data_ptr(), h_mu.data_ptr(), w["t0"], w["tmax"], C.byref(opts),
                                  C.byref(h_out)), "tb_integrate")
@@ -267,6 +275,22 @@ def run_b200(a):
                "h2d_bytes_per_step": int(h_q0.numel() * 8 + h_mu.numel() * 8),
                "d2h_bytes_per_step": int(h_xf.numel() * 8 + h_tf.numel() * 8 + h_ns.numel() * 8 + h_st.numel() * 4),
                "api": "tb_integrate (C ABI, pinned host buffers)"}
+    fast = None
+    if a.mode == "parity" and not a.no_fast:
+        # the same ensemble through the FMA build (TB_MODE_FAST): reported beside the bit-exact headline
+        x_par = d_xf.clone()
+        kcur[0] = tb.Kernel(tape, a.order, L.KIND_PLAIN, L.MODE_FAST)
+        secs_f, kms_f = timed(step_device_k, True)
+        tsf = torch.tensor([float(d_ns.sum().item())], dtype=torch.float64, device=dev)
+        rel = ((d_xf - x_par).abs().amax(0) / x_par.abs().amax(0)).max().reshape(1)
+        if world > 1:
+            dist.all_reduce(tsf, op=dist.ReduceOp.SUM)
+            dist.all_reduce(rel, op=dist.ReduceOp.MAX)
+        fast = {"value": float(tsf.item()) * a.steps / secs_f, "unit": "trajectory-steps/s",
+                "ms_per_step": secs_f / a.steps * 1e3,
+                "roofline_frac": float(tsf.item()) / world * KEPLER_FLOPS_PER_STEP / (float(np.mean(kms_f)) * 1e-3) / 1e12 / peak_tf,
+                "max_rel_diff_final_state_vs_parity": float(rel.item()),
+                "note": "TB_MODE_FAST: FMA + re-associated sums; not bit-identical to the reference order"}
     if rank != 0:
         return
     ms_kernel = float(np.mean(kms))
@@ -283,6 +307,8 @@ def run_b200(a):
                                         "(MEASURED_PEAKS.json has no FP64 entry; nominal 37.2 TFLOP/s)",
                          "kernel": "tb_ensemble_kernel", "kernel_ms": ms_kernel,
                          "pct_of_fp64_peak": 100.0 * ach_tf / peak_tf}}
+    if fast:
+        line["fast_mode"] = fast
     if not a.no_cpu_baseline:
         r, cores, desc, _ = cpu_sample(a, a.cpu_seconds)
         line["cpu_baseline"] = {"value": r, "unit": "trajectory-steps/s", "cores": cores, "kind": "port", "sample": desc}

@@ -187,7 +187,8 @@ typedef struct tb_compile_opts {
 #define TB_CF_NO_PAIRING 16   /* do not emit two consecutive orders of a recurrence together */
 #define TB_CF_NO_GROUPING 32  /* one recurrence entry per group (no interleaving of independent sums) */
 #define TB_CF_NO_QUICK 64     /* parity mode: single jet body with guarded divisions */
-#define TB_CF_STORE_X 256     /* keep state jets stored even when they can be derived from dx */
+#define TB_CF_STORE_X 256     /* fast mode: keep state jets stored even when they can be derived from dx */
+#define TB_CF_DERIVE_X 512    /* parity mode: derive unread state jets from dx (default: stored) */
 #define TB_CF_BLOCK_LOCKSTEP 128 /* barrier per order: the warps of a block share one instruction stream */
 
 /* ---- integration options: keyword arguments of taylorinteg -------------- */

@@ -93,6 +93,7 @@ struct UGen {
         if (!u_is_series(o) || TB_OPERAND_KIND(o) == TB_K_TIME) return;
         ser[o].reads += w;
     }
+    bool derive_x = true;
     void analyse(int reg_budget) {
         const tb_ode_desc_t &d = ode.desc;
         const double w = 0.5 * P * P;
@@ -120,7 +121,7 @@ struct UGen {
             int32_t x = TB_OPERAND(TB_K_X, c), dx = TB_OPERAND(TB_K_DX, c);
             bool cauchy = ser.count(x) && ser[x].reads > 0;
             bool dx_stored = ser.count(dx) && ser[dx].reads > 0;
-            if (!cauchy && dx_stored && !(co.flags & 256)) { ser[x].place = PL_DERIVED; ser[x].id = c; }
+            if (!cauchy && dx_stored && derive_x) { ser[x].place = PL_DERIVED; ser[x].id = c; }
             else ser[x].reads += 0.0; /* creates the entry: stored */
         }
         /* placement by read count */
@@ -708,8 +709,13 @@ int generate_unrolled(const Ode &ode, const tb_compile_opts_t &co, Layout &L, st
     }
     UGen g(ode, co, L);
     const int np1 = co.order + 1;
-    int budget = co.reg_budget > 0 ? co.reg_budget : 3 * np1;
+    /* defaults from the B200 sweeps of round 1: fast mode keeps 3 series in registers
+     * and derives unread state jets; parity mode (more arithmetic per load, Horner on exact quotients) does
+     * better with 4 series in registers and the state jets stored (TB_CF_DERIVE_X overrides)            */
+    const bool parity = co.mode == TB_MODE_PARITY;
+    int budget = co.reg_budget > 0 ? co.reg_budget : (parity ? 4 : 3) * np1;
     if (co.reg_budget < 0) budget = 0;
+    g.derive_x = parity ? (co.flags & 512) != 0 : !(co.flags & 256);
     g.analyse(budget);
     L.variant = 2;
     L.nx = d.dof;
