@@ -289,6 +289,31 @@ int tb_jet(tb_kernel_t *k, int64_t N, const double *q0, const double *params, do
 int tb_dense_eval(int64_t N, int32_t dof, int32_t order, int64_t stride, const double *tv,
                   const double *psol, const int64_t *nsteps, const double *tq, int64_t nq, double *xq);
 
+/* ---- TaylorN jet transport ----------------------------------------------------
+ * taylorinteg with U = TaylorN{Float64} (docs/src/pendulum.md:92-108, test/jettransport.jl;
+ * solcoeff! src/TaylorIntegration.jl:54-65, _norminf src/integrator/stepsize.jl:26-42):
+ * every coefficient of every jet is a polynomial in `nvars` variables truncated at total
+ * degree `varorder`, C(nvars+varorder, varorder) numbers stored by ascending degree and,
+ * inside a degree, in lexicographically descending exponent order (tb_tn_monomials).
+ * q0 / xfinal are [dof x ncoef x N], xv_trange [dof x ncoef x nt x N], trajectory index fastest. */
+typedef struct tb_tn tb_tn_t;
+typedef struct tb_tn_out {
+    double *xfinal;    /* [dof x ncoef x N]                                    */
+    double *tfinal;    /* [N]                                                  */
+    int64_t *nsteps;   /* [N]                                                  */
+    int32_t *status;   /* [N]                                                  */
+    double *xv_trange; /* [dof x ncoef x nt x N], NaN-prefilled (cache.jl:313-316) */
+} tb_tn_out_t;
+tb_tn_t *tb_tn_create(const tb_ode_t *ode, int order, int nvars, int varorder, int mode);
+void tb_tn_free(tb_tn_t *t);
+int tb_tn_ncoef(const tb_tn_t *t);
+/* exponents [ncoef x nvars] of the flat coefficient order; returns ncoef        */
+int tb_tn_monomials(const tb_tn_t *t, int32_t *expo);
+/* HOST buffers. trange == NULL: (t0,tmax) driver (taylorinteg.jl:329-381); else the
+ * trange driver (582-642) on the sorted grid trange[nt].                        */
+int tb_tn_integrate(tb_tn_t *t, int64_t N, const double *q0, const double *params, double t0, double tmax,
+                    const double *trange, int64_t nt, const tb_opts_t *opts, const tb_tn_out_t *out);
+
 /* FP64 roofline probe: register-only DFMA chains on the current device.
  * Returns achieved TFLOP/s (2 flops per DFMA) over >= `seconds` of work.     */
 int tb_fp64_peak(double seconds, double *tflops, double *ms);

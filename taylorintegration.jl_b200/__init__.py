@@ -8,7 +8,9 @@ from ._lib import TaylorB200Error  # noqa: F401
 from .tape import Tape, taylorize, sin, cos, sqrt, exp, log, zero  # noqa: F401
 from .api import (EnsembleSolution, Kernel, TaylorSolution, fp64_peak, get_kernel, lyap_taylorinteg, make_opts,  # noqa: F401
                   taylorinteg, taylorinteg_events)
+from .jettransport import JetSolution, JetTransport, taylorinteg_jet  # noqa: F401
 from . import problems  # noqa: F401
 
 __all__ = ["taylorinteg", "lyap_taylorinteg", "taylorize", "TaylorSolution", "EnsembleSolution", "Kernel", "Tape",
-           "sin", "cos", "sqrt", "exp", "log", "zero", "fp64_peak", "problems", "TaylorB200Error"]
+           "sin", "cos", "sqrt", "exp", "log", "zero", "fp64_peak", "problems", "TaylorB200Error",
+           "JetTransport", "JetSolution", "taylorinteg_jet"]

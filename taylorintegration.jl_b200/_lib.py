@@ -89,7 +89,13 @@ EXPORTS = [
     "tb_generate_source", "tb_compile", "tb_kernel_free", "tb_kernel_source", "tb_kernel_log", "tb_kernel_info",
     "tb_kernel_cubin", "tb_integrate", "tb_integrate_trange", "tb_work_bytes", "tb_integrate_device",
     "tb_launch_count", "tb_jet", "tb_dense_eval", "tb_fp64_peak", "tb_device_count", "tb_set_device",
+    "tb_tn_create", "tb_tn_free", "tb_tn_ncoef", "tb_tn_monomials", "tb_tn_integrate",
 ]
+
+
+class TbTnOut(C.Structure):
+    _fields_ = [("xfinal", _DP), ("tfinal", _DP), ("nsteps", C.POINTER(C.c_int64)), ("status", C.POINTER(C.c_int32)),
+                ("xv_trange", _DP)]
 
 
 class TaylorB200Error(RuntimeError):
@@ -139,6 +145,13 @@ def lib() -> C.CDLL:
     L.tb_dense_eval.argtypes = [C.c_int64, C.c_int32, C.c_int32, C.c_int64, vp, vp, vp, vp, C.c_int64, vp]
     L.tb_fp64_peak.argtypes = [C.c_double, _DP, _DP]
     L.tb_set_device.argtypes = [C.c_int]
+    L.tb_tn_create.restype = vp
+    L.tb_tn_create.argtypes = [vp, C.c_int, C.c_int, C.c_int, C.c_int]
+    L.tb_tn_free.argtypes = [vp]
+    L.tb_tn_ncoef.argtypes = [vp]
+    L.tb_tn_monomials.argtypes = [vp, vp]
+    L.tb_tn_integrate.argtypes = [vp, C.c_int64, vp, vp, C.c_double, C.c_double, vp, C.c_int64, C.POINTER(TbOpts),
+                                  C.POINTER(TbTnOut)]
     _lib = L
     return L
 

@@ -1,0 +1,556 @@
+/*
+ * tb_tn.cu -- TaylorN jet transport on sm_100a: taylorinteg with U = TaylorN{Float64}
+ * (reference: dispatch of src/integrator/taylorinteg.jl:329-381 / 582-642 on polynomial-valued
+ * coefficients; solcoeff! src/TaylorIntegration.jl:54-65; _norminf src/integrator/stepsize.jl:26-42).
+ *
+ * One CTA integrates one trajectory (persistent CTAs pull trajectory indices from a queue); thread m
+ * owns polynomial coefficient m of every series.  All products are GATHERS: the thread sums
+ * U[ia]*V[ib] over the precomputed pairs with mono[ia]+mono[ib] = mono[m], in ascending ia -- the
+ * order in which TaylorSeries' scatter loops touch slot m (tb_tn_tables.h) -- so no atomics, no
+ * write conflicts, and in parity mode the same bits as oracle/tb_tn_oracle.cpp.  Recurrences over
+ * homogeneous degree (TaylorN division, power, sincos) advance one degree per barrier.
+ * The tape is interpreted (each entry costs thousands of FMAs, dispatch is free).  Jets live in a
+ * per-CTA workspace in global memory: (2 dof + ntmp + 1) series x (P+1) x ncoef doubles
+ * (pendulum n=2: 60 KB, L1-resident; Kepler n=4 order 8: ~2 MB, L2-resident).
+ */
+#include <cuda_runtime.h>
+
+#include <cstdint>
+#include <string>
+#include <vector>
+
+#include "tb_internal.h"
+#include "tb_math.h"
+#include "tb_tn_tables.h"
+
+namespace tb {
+void count_launch(long long n);
+}
+struct tb_ode {
+    tb::Ode o;
+};
+
+namespace {
+
+#define TB_CUDA(call)                                                          \
+    do {                                                                       \
+        cudaError_t e_ = (call);                                               \
+        if (e_ != cudaSuccess) {                                               \
+            tb::set_error(std::string(#call) + ": " + cudaGetErrorString(e_)); \
+            return TB_ERR_CUDA;                                                \
+        }                                                                      \
+    } while (0)
+
+struct TnArgs {
+    long long N;
+    int dof, npar, ntmp, nops, P, nc, d, nser;
+    const tb_op_t *ops;
+    const unsigned char *deg;     /* [nc] */
+    const int *pair_off;          /* [nc+1] */
+    const unsigned short *pair_a; /* pairs of slot m, ascending ia */
+    const unsigned short *pair_b;
+    const double *q0;     /* [dof x nc x N] */
+    const double *params; /* [npar x N] or [npar] */
+    const double *trange;
+    long long nt;
+    double t0, tmax, abstol, reltol, minstep, maxstep;
+    long long maxsteps;
+    int params_per_traj;
+    double *work; /* [gridDim.x][nser][P+1][nc] */
+    double *xfinal, *tfinal;
+    long long *nsteps;
+    int *status;
+    double *xv_trange; /* [dof x nc x nt x N] */
+    unsigned long long *counter;
+};
+
+template <bool FAST> __device__ __forceinline__ double mad(double a, double b, double c) {
+    return FAST ? fma(a, b, c) : __dadd_rn(c, __dmul_rn(a, b));
+}
+
+/* per-CTA view of the jets */
+struct Jets {
+    double *base;
+    int P, nc, dof, ntmp;
+    __device__ __forceinline__ double *ser(int o) const {
+        const int kind = TB_OPERAND_KIND(o), idx = TB_OPERAND_INDEX(o);
+        int s = 0;
+        if (kind == TB_K_X) s = idx;
+        else if (kind == TB_K_DX) s = dof + idx;
+        else if (kind == TB_K_TMP) s = 2 * dof + idx;
+        else s = 2 * dof + ntmp; /* TB_K_TIME */
+        return base + (size_t)s * (P + 1) * nc;
+    }
+    __device__ __forceinline__ double *co(int o, int k) const { return ser(o) + (size_t)k * nc; }
+};
+
+/* acc += sum over the pairs [p0, p1) of slot m of (f*U[ia]) * V[ib] */
+template <bool FAST>
+__device__ __forceinline__ double gather(double acc, const TnArgs &a, int p0, int p1, const double *__restrict__ U,
+                                         const double *__restrict__ V, bool hasf, double f) {
+    for (int p = p0; p < p1; p++) {
+        const int ia = __ldg(a.pair_a + p), ib = __ldg(a.pair_b + p);
+        double u = U[ia];
+        if (hasf) u = __dmul_rn(f, u);
+        acc = mad<FAST>(u, V[ib], acc);
+    }
+    return acc;
+}
+
+/* Q = Nn / B over homogeneous degree; nn = Nn[m] in a register.  Q_g = (Nn_g - sum_{j<g} Q_j B_{g-j}) / B_0 */
+template <bool FAST>
+__device__ void tn_div(const TnArgs &a, int m, int degm, double *Q, double nn, const double *B) {
+    const bool act = m < a.nc;
+    const int p0 = act ? a.pair_off[m] : 0, p1 = act ? a.pair_off[m + 1] - 1 : 0; /* last pair is (m, 0) */
+    for (int g = 0; g <= a.d; g++) {
+        if (act && degm == g) {
+            const double t = gather<FAST>(0.0, a, p0, p1, Q, B, false, 0.0);
+            Q[m] = __ddiv_rn(__dsub_rn(nn, t), B[0]);
+        }
+        __syncthreads();
+    }
+}
+
+/* C = A^r: C_0 = A_0^r; C_g = sum_{j<g} ((r(g-j) - j) C_j) A_{g-j} / (g A_0) */
+template <bool FAST>
+__device__ void tn_pow(const TnArgs &a, int m, int degm, double *C, const double *A, double r) {
+    const bool act = m < a.nc;
+    if (m == 0) C[0] = tb_pow(A[0], r);
+    __syncthreads();
+    const int p0 = act ? a.pair_off[m] : 0, p1 = act ? a.pair_off[m + 1] - 1 : 0;
+    for (int g = 1; g <= a.d; g++) {
+        if (act && degm == g) {
+            double t = 0.0;
+            for (int p = p0; p < p1; p++) {
+                const int ia = __ldg(a.pair_a + p), ib = __ldg(a.pair_b + p);
+                const int j = a.deg[ia];
+                const double f = __dsub_rn(__dmul_rn(r, (double)(g - j)), (double)j);
+                t = mad<FAST>(__dmul_rn(f, C[ia]), A[ib], t);
+            }
+            C[m] = __ddiv_rn(t, __dmul_rn((double)g, A[0]));
+        }
+        __syncthreads();
+    }
+}
+
+/* S = sin A, Cc = cos A: S_g = sum_{j>=1} (j A_j) Cc_{g-j} / g, Cc_g = -sum_{j>=1} (j A_j) S_{g-j} / g */
+template <bool FAST>
+__device__ void tn_sincos(const TnArgs &a, int m, int degm, double *S, double *Cc, const double *A) {
+    const bool act = m < a.nc;
+    if (m == 0) { double s, c; tb_sincos(A[0], &s, &c); S[0] = s; Cc[0] = c; }
+    __syncthreads();
+    const int p0 = act ? a.pair_off[m] + 1 : 0, p1 = act ? a.pair_off[m + 1] : 0; /* first pair is (0, m) */
+    for (int g = 1; g <= a.d; g++) {
+        if (act && degm == g) {
+            double ts = 0.0, tc = 0.0;
+            for (int p = p0; p < p1; p++) {
+                const int ia = __ldg(a.pair_a + p), ib = __ldg(a.pair_b + p);
+                const int j = a.deg[ia];
+                double u = A[ia];
+                if (j >= 2) u = __dmul_rn((double)j, u);
+                ts = mad<FAST>(u, Cc[ib], ts);
+                tc = mad<FAST>(u, S[ib], tc);
+            }
+            S[m] = __ddiv_rn(ts, (double)g);
+            Cc[m] = __ddiv_rn(-tc, (double)g);
+        }
+        __syncthreads();
+    }
+}
+
+/* one tape entry at time order k; every thread of the CTA calls it; ends with a barrier */
+template <bool FAST>
+__device__ void run_op(const TnArgs &a, const Jets &J, const double *par, double *scratch, const tb_op_t &op, int k,
+                       int m, int degm) {
+    const int ka = TB_OPERAND_KIND(op.a), kb = TB_OPERAND_KIND(op.b);
+    const bool sa = ka == TB_K_PAR || ka == TB_K_IMM, sb = kb == TB_K_PAR || kb == TB_K_IMM;
+    const double na = ka == TB_K_PAR ? par[TB_OPERAND_INDEX(op.a)] : op.imm;
+    const double nb = kb == TB_K_PAR ? par[TB_OPERAND_INDEX(op.b)] : op.imm;
+    const bool act = m < a.nc;
+    double *R = J.co(op.res, k);
+    const int p0 = act ? a.pair_off[m] : 0, p1 = act ? a.pair_off[m + 1] : 0;
+    int opc = op.op;
+    if (opc == TB_OP_POW) {
+        if (op.imm == 1.0) opc = TB_OP_IDENTITY;
+        else if (op.imm == 2.0) opc = TB_OP_SQR;
+    }
+    switch (opc) {
+        case TB_OP_IDENTITY:
+            if (act) R[m] = sa ? ((k == 0 && m == 0) ? na : 0.0) : J.co(op.a, k)[m];
+            break;
+        case TB_OP_NEG:
+            if (act) R[m] = -J.co(op.a, k)[m];
+            break;
+        case TB_OP_ADD:
+        case TB_OP_SUB:
+            if (act) {
+                const bool add = opc == TB_OP_ADD, c0 = k == 0 && m == 0;
+                double v;
+                if (sa && sb) v = c0 ? (add ? __dadd_rn(na, nb) : __dsub_rn(na, nb)) : 0.0;
+                else if (sa) { const double b = J.co(op.b, k)[m]; v = c0 ? (add ? __dadd_rn(na, b) : __dsub_rn(na, b)) : (add ? b : -b); }
+                else if (sb) { const double x = J.co(op.a, k)[m]; v = c0 ? (add ? __dadd_rn(x, nb) : __dsub_rn(x, nb)) : x; }
+                else { const double x = J.co(op.a, k)[m], b = J.co(op.b, k)[m]; v = add ? __dadd_rn(x, b) : __dsub_rn(x, b); }
+                R[m] = v;
+            }
+            break;
+        case TB_OP_MUL:
+            if (act) {
+                if (sa && sb) R[m] = (k == 0 && m == 0) ? __dmul_rn(na, nb) : 0.0;
+                else if (sa || sb) R[m] = __dmul_rn(sa ? na : nb, J.co(sa ? op.b : op.a, k)[m]);
+                else {
+                    double acc = 0.0;
+                    for (int i = 0; i <= k; i++) acc = gather<FAST>(acc, a, p0, p1, J.co(op.a, i), J.co(op.b, k - i), false, 0.0);
+                    R[m] = acc;
+                }
+            }
+            break;
+        case TB_OP_SQR:
+            if (act) {
+                double acc = 0.0;
+                if (k == 0) acc = gather<FAST>(acc, a, p0, p1, J.co(op.a, 0), J.co(op.a, 0), false, 0.0);
+                else {
+                    const int kodd = k & 1, kend = (k - 2 + kodd) / 2;
+                    for (int i = 0; i <= kend; i++) acc = gather<FAST>(acc, a, p0, p1, J.co(op.a, i), J.co(op.a, k - i), false, 0.0);
+                    acc = __dmul_rn(2.0, acc);
+                    if (!kodd) acc = gather<FAST>(acc, a, p0, p1, J.co(op.a, k / 2), J.co(op.a, k / 2), false, 0.0);
+                }
+                R[m] = acc;
+            }
+            break;
+        case TB_OP_DIV:
+            if (sb) {
+                if (act) R[m] = sa ? ((k == 0 && m == 0) ? __ddiv_rn(na, nb) : 0.0) : __ddiv_rn(J.co(op.a, k)[m], nb);
+            } else {
+                double nn = 0.0;
+                if (act) {
+                    double t = 0.0;
+                    for (int i = 0; i < k; i++) t = gather<FAST>(t, a, p0, p1, J.co(op.res, i), J.co(op.b, k - i), false, 0.0);
+                    const double num = sa ? ((k == 0 && m == 0) ? na : 0.0) : J.co(op.a, k)[m];
+                    nn = __dsub_rn(num, t);
+                }
+                tn_div<FAST>(a, m, degm, R, nn, J.co(op.b, 0));
+            }
+            break;
+        case TB_OP_POW:
+            if (k == 0) tn_pow<FAST>(a, m, degm, R, J.co(op.a, 0), op.imm);
+            else {
+                double t = 0.0;
+                if (act) {
+                    for (int i = 0; i < k; i++) {
+                        const double f = __dsub_rn(__dmul_rn(op.imm, (double)(k - i)), (double)i);
+                        t = gather<FAST>(t, a, p0, p1, J.co(op.res, i), J.co(op.a, k - i), true, f);
+                    }
+                    scratch[m] = __dmul_rn((double)k, J.co(op.a, 0)[m]);
+                }
+                __syncthreads();
+                tn_div<FAST>(a, m, degm, R, t, scratch);
+            }
+            break;
+        case TB_OP_SINCOS: {
+            double *Cc = J.co(op.aux, k);
+            if (k == 0) tn_sincos<FAST>(a, m, degm, R, Cc, J.co(op.a, 0));
+            else if (act) {
+                double ts = 0.0, tc = 0.0;
+                for (int i = 1; i <= k; i++) {
+                    ts = gather<FAST>(ts, a, p0, p1, J.co(op.a, i), J.co(op.aux, k - i), i >= 2, (double)i);
+                    tc = gather<FAST>(tc, a, p0, p1, J.co(op.a, i), J.co(op.res, k - i), i >= 2, (double)i);
+                }
+                R[m] = __ddiv_rn(ts, (double)k);
+                Cc[m] = __ddiv_rn(-tc, (double)k);
+            }
+            break;
+        }
+        default: break; /* rejected on the host */
+    }
+    __syncthreads();
+}
+
+/* block-wide max of |v| (order-independent, so bit-identical to the oracle's sequential _norminf) */
+__device__ double block_max(double v, double *red) {
+    for (int o = 16; o > 0; o >>= 1) v = fmax(v, __shfl_xor_sync(0xffffffffu, v, o));
+    const int w = threadIdx.x >> 5, nw = (blockDim.x + 31) >> 5;
+    __syncthreads();
+    if ((threadIdx.x & 31) == 0) red[w] = v;
+    __syncthreads();
+    double r = red[0];
+    for (int i = 1; i < nw; i++) r = fmax(r, red[i]);
+    return r;
+}
+
+template <bool FAST> __global__ void __launch_bounds__(1024) tn_kernel(const TnArgs a) {
+    __shared__ double red[32];
+    __shared__ unsigned long long s_idx;
+    extern __shared__ double scratch[]; /* [nc] */
+    const int m = threadIdx.x, nc = a.nc, P = a.P;
+    const bool act = m < nc;
+    const int degm = act ? a.deg[m] : -1;
+    Jets J{a.work + (size_t)blockIdx.x * a.nser * (P + 1) * nc, P, nc, a.dof, a.ntmp};
+    const int TIME = TB_OPERAND(TB_K_TIME, 0);
+    const double inf = __longlong_as_double(0x7FF0000000000000LL), nan = __longlong_as_double(0x7FF8000000000000LL);
+    for (;;) {
+        if (m == 0) s_idx = atomicAdd(a.counter, 1ull);
+        __syncthreads();
+        const long long i = (long long)s_idx;
+        __syncthreads();
+        if (i >= a.N) break;
+        double par[8];
+        for (int j = 0; j < a.npar && j < 8; j++) par[j] = a.params_per_traj ? a.params[(long long)j * a.N + i] : a.params[j];
+        /* init_expansions / update_cache!: cache.jl:176-192, 435-442 */
+        if (act) {
+            for (int c = 0; c < a.dof; c++) J.co(TB_OPERAND(TB_K_X, c), 0)[m] = a.q0[((long long)c * nc + m) * a.N + i];
+            for (int k = 0; k <= P; k++) J.co(TIME, k)[m] = (k == 1 && m == 0) ? 1.0 : 0.0;
+        }
+        double t0 = a.trange ? a.trange[0] : a.t0;
+        const double tmax = a.trange ? a.trange[a.nt - 1] : a.tmax;
+        const double sign = copysign(1.0, __dsub_rn(tmax, t0));
+        long long nsteps = 1, iter = 2;
+        double t1 = a.trange ? a.trange[1] : 0.0;
+        int st = 0;
+        if (a.trange && a.xv_trange && act)
+            for (int c = 0; c < a.dof; c++) {
+                a.xv_trange[(((long long)c * nc + m) * a.nt) * a.N + i] = J.co(TB_OPERAND(TB_K_X, c), 0)[m];
+                for (long long j = 1; j < a.nt; j++) a.xv_trange[(((long long)c * nc + m) * a.nt + j) * a.N + i] = nan;
+            }
+        __syncthreads();
+        while (__dmul_rn(sign, t0) < __dmul_rn(sign, tmax)) {
+            /* jetcoeffs!: parse_eqs.jl:259-264, solcoeff! TaylorIntegration.jl:54-65 */
+            if (m == 0) J.co(TIME, 0)[0] = t0;
+            __syncthreads();
+            for (int k = 0; k < P; k++) {
+                for (int j = 0; j < a.nops; j++) run_op<FAST>(a, J, par, scratch, a.ops[j], k, m, degm);
+                if (act)
+                    for (int c = 0; c < a.dof; c++)
+                        J.co(TB_OPERAND(TB_K_X, c), k + 1)[m] = __ddiv_rn(J.co(TB_OPERAND(TB_K_DX, c), k)[m], (double)(k + 1));
+                __syncthreads();
+            }
+            /* stepsize: stepsize.jl:58-99 with _norminf (26-42) = max |coefficient| */
+            double h = inf;
+            for (int c = 0; c < a.dof; c++) {
+                const int X = TB_OPERAND(TB_K_X, c);
+                const double x0norm = block_max(act ? fabs(J.co(X, 0)[m]) : 0.0, red);
+                for (int k = P - 1; k <= P; k++) {
+                    const double nk = block_max(act ? fabs(J.co(X, k)[m]) : 0.0, red);
+                    if (nk == 0.0) continue;
+                    const double rel = __dmul_rn(a.reltol, x0norm);
+                    const double eps = a.abstol >= rel ? a.abstol : rel;
+                    h = fmin(h, tb_pow(__ddiv_rn(eps, nk), __ddiv_rn(1.0, (double)k)));
+                }
+            }
+            if (h == inf) { /* _second_stepsize: stepsize.jl:119-132 */
+                h = 0.0;
+                for (int c = 0; c < a.dof; c++) {
+                    const int X = TB_OPERAND(TB_K_X, c);
+                    double hc = 0.0;
+                    bool allzero = block_max(act ? fabs(J.co(X, 0)[m]) : 0.0, red) == 0.0 &&
+                                   block_max(act ? fabs(J.co(X, P - 1)[m]) : 0.0, red) == 0.0 &&
+                                   block_max(act ? fabs(J.co(X, P)[m]) : 0.0, red) == 0.0;
+                    for (int k = 1; k <= P - 2; k++) {
+                        const double nk = block_max(act ? fabs(J.co(X, k)[m]) : 0.0, red);
+                        if (nk == 0.0) continue;
+                        allzero = false;
+                        hc = fmax(hc, tb_pow(__ddiv_rn(1.0, nk), __ddiv_rn(1.0, (double)k)));
+                    }
+                    h = fmax(h, allzero ? inf : hc);
+                }
+            }
+            double dt = h < a.minstep ? a.minstep : (h > a.maxstep ? a.maxstep : h);
+            if (dt == 0.0) { st |= TB_ST_ZERO_STEP; break; }
+            const double rem = __dsub_rn(tmax, t0);
+            dt = __dmul_rn(sign, fmin(dt, __dmul_rn(sign, rem)));
+            double xn[16];
+            bool fin = true;
+            if (act)
+                for (int c = 0; c < a.dof; c++) {
+                    const double *X = J.ser(TB_OPERAND(TB_K_X, c));
+                    double s = X[(size_t)P * nc + m];
+                    for (int k = P - 1; k >= 0; k--) s = __dadd_rn(__dmul_rn(s, dt), X[(size_t)k * nc + m]);
+                    xn[c] = s;
+                    fin = fin && isfinite(s);
+                }
+            bool done = false;
+            if (a.trange) {
+                const double tnext = __dadd_rn(t0, dt);
+                while (__dmul_rn(sign, t1) < __dmul_rn(sign, tnext)) {
+                    const double d1 = __dsub_rn(t1, t0);
+                    if (act && a.xv_trange)
+                        for (int c = 0; c < a.dof; c++) {
+                            const double *X = J.ser(TB_OPERAND(TB_K_X, c));
+                            double s = X[(size_t)P * nc + m];
+                            for (int k = P - 1; k >= 0; k--) s = __dadd_rn(__dmul_rn(s, d1), X[(size_t)k * nc + m]);
+                            a.xv_trange[(((long long)c * nc + m) * a.nt + (iter - 1)) * a.N + i] = s;
+                        }
+                    iter += 1;
+                    t1 = a.trange[iter - 1];
+                }
+                if (dt == rem) {
+                    if (act && a.xv_trange)
+                        for (int c = 0; c < a.dof; c++) a.xv_trange[(((long long)c * nc + m) * a.nt + (iter - 1)) * a.N + i] = xn[c];
+                    done = true;
+                }
+                t0 = tnext;
+            } else
+                t0 = __dadd_rn(t0, dt);
+            __syncthreads(); /* every thread has read the old jets */
+            if (act)
+                for (int c = 0; c < a.dof; c++) J.co(TB_OPERAND(TB_K_X, c), 0)[m] = xn[c];
+            if (done) break;
+            nsteps += 1;
+            if (nsteps > a.maxsteps) { st |= TB_ST_MAXSTEPS; break; }
+            if (__syncthreads_or(!fin)) { st |= TB_ST_NONFINITE; break; }
+        }
+        __syncthreads();
+        if (act && a.xfinal)
+            for (int c = 0; c < a.dof; c++) a.xfinal[((long long)c * nc + m) * a.N + i] = J.co(TB_OPERAND(TB_K_X, c), 0)[m];
+        if (m == 0) {
+            if (a.tfinal) a.tfinal[i] = t0;
+            if (a.nsteps) a.nsteps[i] = nsteps - 1;
+            if (a.status) a.status[i] = st;
+        }
+        __syncthreads();
+    }
+}
+
+} // namespace
+
+/* ---- host side ------------------------------------------------------------------------------------ */
+struct tb_tn {
+    tb::Ode ode;
+    int order = 0, nvars = 0, varorder = 0, mode = 0;
+    tbtn::Tables T;
+    /* device copies (current device of the first integrate call) */
+    int device = -1;
+    tb_op_t *d_ops = nullptr;
+    unsigned char *d_deg = nullptr;
+    int *d_off = nullptr;
+    unsigned short *d_pa = nullptr, *d_pb = nullptr;
+};
+
+extern "C" {
+
+tb_tn_t *tb_tn_create(const tb_ode_t *ode, int order, int nvars, int varorder, int mode) {
+    if (!ode || order < 1 || order > 60 || nvars < 1 || nvars > 8 || varorder < 0 || varorder > 20) {
+        tb::set_error("tb_tn_create: bad argument");
+        return nullptr;
+    }
+    const tb_ode_desc_t &d = ode->o.desc;
+    if (d.dof > 16 || d.npar > 8) { tb::set_error("tb_tn_create: dof <= 16 and npar <= 8 supported"); return nullptr; }
+    for (int j = 0; j < d.nops; j++) {
+        const tb_op_t &op = ode->o.ops[j];
+        const int ka = TB_OPERAND_KIND(op.a);
+        const bool sa = ka == TB_K_PAR || ka == TB_K_IMM;
+        bool ok = false;
+        switch (op.op) {
+            case TB_OP_IDENTITY: case TB_OP_ADD: case TB_OP_SUB: case TB_OP_MUL: case TB_OP_DIV: ok = true; break;
+            case TB_OP_NEG: case TB_OP_SQR: case TB_OP_POW: case TB_OP_SINCOS: ok = !sa; break;
+            default: break;
+        }
+        if (!ok) { tb::set_error("tb_tn_create: tape entry " + std::to_string(j) + " has no TaylorN kernel yet (supported: identity, neg, add, sub, mul, div, sqr, pow, sincos)"); return nullptr; }
+    }
+    tb_tn *t = new tb_tn;
+    t->ode = ode->o;
+    t->ode.desc.ops = t->ode.ops.data();
+    t->order = order; t->nvars = nvars; t->varorder = varorder; t->mode = mode;
+    t->T = tbtn::make_tables(nvars, varorder);
+    if (t->T.ncoef > 1024) { tb::set_error("tb_tn_create: more than 1024 polynomial coefficients"); delete t; return nullptr; }
+    return t;
+}
+
+void tb_tn_free(tb_tn_t *t) {
+    if (!t) return;
+    if (t->d_ops) { cudaFree(t->d_ops); cudaFree(t->d_deg); cudaFree(t->d_off); cudaFree(t->d_pa); cudaFree(t->d_pb); }
+    delete t;
+}
+
+int tb_tn_ncoef(const tb_tn_t *t) { return t ? t->T.ncoef : TB_ERR_ARG; }
+
+int tb_tn_monomials(const tb_tn_t *t, int32_t *expo) {
+    if (!t || !expo) return TB_ERR_ARG;
+    for (size_t i = 0; i < t->T.expo.size(); i++) expo[i] = t->T.expo[i];
+    return t->T.ncoef;
+}
+
+int tb_tn_integrate(tb_tn_t *t, int64_t N, const double *q0, const double *params, double t0, double tmax,
+                    const double *trange, int64_t nt, const tb_opts_t *o, const tb_tn_out_t *out) {
+    if (!t || !q0 || !o || !out || N < 0 || (trange && nt < 2)) { tb::set_error("tb_tn_integrate: bad argument"); return TB_ERR_ARG; }
+    if (N == 0) return TB_OK;
+    int dev = 0;
+    TB_CUDA(cudaGetDevice(&dev));
+    const tb_ode_desc_t &d = t->ode.desc;
+    const int nc = t->T.ncoef, P = t->order;
+    if (!t->d_ops || t->device != dev) {
+        t->device = dev;
+        TB_CUDA(cudaMalloc(&t->d_ops, sizeof(tb_op_t) * (d.nops > 0 ? d.nops : 1)));
+        TB_CUDA(cudaMemcpy(t->d_ops, t->ode.ops.data(), sizeof(tb_op_t) * d.nops, cudaMemcpyHostToDevice));
+        TB_CUDA(cudaMalloc(&t->d_deg, nc));
+        TB_CUDA(cudaMemcpy(t->d_deg, t->T.deg.data(), nc, cudaMemcpyHostToDevice));
+        TB_CUDA(cudaMalloc(&t->d_off, sizeof(int) * (nc + 1)));
+        TB_CUDA(cudaMemcpy(t->d_off, t->T.pair_off.data(), sizeof(int) * (nc + 1), cudaMemcpyHostToDevice));
+        const size_t np = t->T.pair_a.size();
+        TB_CUDA(cudaMalloc(&t->d_pa, 2 * np));
+        TB_CUDA(cudaMalloc(&t->d_pb, 2 * np));
+        TB_CUDA(cudaMemcpy(t->d_pa, t->T.pair_a.data(), 2 * np, cudaMemcpyHostToDevice));
+        TB_CUDA(cudaMemcpy(t->d_pb, t->T.pair_b.data(), 2 * np, cudaMemcpyHostToDevice));
+    }
+    const int threads = ((nc + 31) / 32) * 32;
+    const size_t smem = sizeof(double) * nc;
+    const bool fast = t->mode == TB_MODE_FAST;
+    int bps = 1, nsm = 148;
+    if (fast) TB_CUDA(cudaOccupancyMaxActiveBlocksPerMultiprocessor(&bps, tn_kernel<true>, threads, smem));
+    else TB_CUDA(cudaOccupancyMaxActiveBlocksPerMultiprocessor(&bps, tn_kernel<false>, threads, smem));
+    TB_CUDA(cudaDeviceGetAttribute(&nsm, cudaDevAttrMultiProcessorCount, dev));
+    if (bps < 1) bps = 1;
+    if (bps > 16) bps = 16;
+    long long blocks = (long long)nsm * bps;
+    if (blocks > N) blocks = N;
+    TnArgs a{};
+    a.N = N; a.dof = d.dof; a.npar = d.npar; a.ntmp = d.ntmp; a.nops = d.nops; a.P = P; a.nc = nc; a.d = t->varorder;
+    a.nser = 2 * d.dof + d.ntmp + 1;
+    a.ops = t->d_ops; a.deg = t->d_deg; a.pair_off = t->d_off; a.pair_a = t->d_pa; a.pair_b = t->d_pb;
+    a.nt = trange ? nt : 0; a.t0 = t0; a.tmax = tmax; a.abstol = o->abstol; a.reltol = o->reltol;
+    a.minstep = o->minstepsize; a.maxstep = o->maxstepsize; a.maxsteps = o->maxsteps; a.params_per_traj = o->params_per_traj;
+    const size_t nq = (size_t)d.dof * nc * N, npar = (size_t)(d.npar > 0 ? d.npar : 1) * (o->params_per_traj ? N : 1);
+    double *dq = nullptr, *dp = nullptr, *dtr = nullptr, *dwork = nullptr, *dxf = nullptr, *dtf = nullptr, *dxv = nullptr;
+    long long *dns = nullptr; int *dst = nullptr; unsigned long long *dctr = nullptr;
+    int rc = TB_OK;
+    auto fail = [&](cudaError_t e, const char *what) { if (e != cudaSuccess && rc == TB_OK) { tb::set_error(std::string(what) + ": " + cudaGetErrorString(e)); rc = TB_ERR_CUDA; } };
+    fail(cudaMalloc(&dq, 8 * nq), "cudaMalloc q0");
+    fail(cudaMalloc(&dp, 8 * npar), "cudaMalloc params");
+    fail(cudaMalloc(&dwork, 8 * (size_t)blocks * a.nser * (P + 1) * nc), "cudaMalloc workspace");
+    fail(cudaMalloc(&dxf, 8 * nq), "cudaMalloc xfinal");
+    fail(cudaMalloc(&dtf, 8 * N), "cudaMalloc tfinal");
+    fail(cudaMalloc(&dns, 8 * N), "cudaMalloc nsteps");
+    fail(cudaMalloc(&dst, 4 * N), "cudaMalloc status");
+    fail(cudaMalloc(&dctr, 8), "cudaMalloc counter");
+    if (trange) {
+        fail(cudaMalloc(&dtr, 8 * nt), "cudaMalloc trange");
+        if (out->xv_trange) fail(cudaMalloc(&dxv, 8 * nq * nt), "cudaMalloc xv_trange");
+    }
+    if (rc == TB_OK) {
+        fail(cudaMemcpy(dq, q0, 8 * nq, cudaMemcpyHostToDevice), "copy q0");
+        if (d.npar > 0 && params) fail(cudaMemcpy(dp, params, 8 * npar, cudaMemcpyHostToDevice), "copy params");
+        if (trange) fail(cudaMemcpy(dtr, trange, 8 * nt, cudaMemcpyHostToDevice), "copy trange");
+        fail(cudaMemset(dctr, 0, 8), "memset counter");
+        fail(cudaMemset(dwork, 0, 8 * (size_t)blocks * a.nser * (P + 1) * nc), "memset workspace");
+        a.q0 = dq; a.params = dp; a.trange = trange ? dtr : nullptr; a.work = dwork; a.xfinal = dxf; a.tfinal = dtf;
+        a.nsteps = dns; a.status = dst; a.xv_trange = dxv; a.counter = dctr;
+    }
+    if (rc == TB_OK) {
+        if (fast) tn_kernel<true><<<(unsigned)blocks, threads, smem>>>(a);
+        else tn_kernel<false><<<(unsigned)blocks, threads, smem>>>(a);
+        tb::count_launch(1);
+        fail(cudaGetLastError(), "tn_kernel launch");
+        fail(cudaDeviceSynchronize(), "tn_kernel");
+    }
+    if (rc == TB_OK) {
+        if (out->xfinal) fail(cudaMemcpy(out->xfinal, dxf, 8 * nq, cudaMemcpyDeviceToHost), "copy xfinal");
+        if (out->tfinal) fail(cudaMemcpy(out->tfinal, dtf, 8 * N, cudaMemcpyDeviceToHost), "copy tfinal");
+        if (out->nsteps) fail(cudaMemcpy(out->nsteps, dns, 8 * N, cudaMemcpyDeviceToHost), "copy nsteps");
+        if (out->status) fail(cudaMemcpy(out->status, dst, 4 * N, cudaMemcpyDeviceToHost), "copy status");
+        if (out->xv_trange && dxv) fail(cudaMemcpy(out->xv_trange, dxv, 8 * nq * nt, cudaMemcpyDeviceToHost), "copy xv_trange");
+    }
+    cudaFree(dq); cudaFree(dp); cudaFree(dtr); cudaFree(dwork); cudaFree(dxf); cudaFree(dtf); cudaFree(dxv);
+    cudaFree(dns); cudaFree(dst); cudaFree(dctr);
+    return rc;
+}
+
+} /* extern "C" */

@@ -135,3 +135,56 @@ def integrate(tape: tb.Tape, order: int, q0, t0=0.0, tmax=None, params=None, *, 
     assert rc == 0, rc
     del keep
     return sol
+
+
+# ---- TaylorN jet transport oracle (oracle/libtb_tn_oracle.so) -----------------------------------------------
+_SO_TN = os.path.join(_ROOT, "oracle", "libtb_tn_oracle.so")
+_lib_tn = None
+
+
+def lib_tn() -> C.CDLL:
+    global _lib_tn
+    if _lib_tn is None:
+        if not os.path.exists(_SO_TN):
+            build()
+        o = C.CDLL(_SO_TN)
+        vp = C.c_void_p
+        o.tbo_tn_monomials.argtypes = [C.c_int, C.c_int, vp]
+        o.tbo_tn_integrate.argtypes = [C.POINTER(L.TbOdeDesc), C.c_int, C.c_int, C.c_int, C.c_int64, vp, vp, C.c_double,
+                                       C.c_double, vp, C.c_int64, C.POINTER(L.TbOpts), vp, vp, vp, vp, vp]
+        _lib_tn = o
+    return _lib_tn
+
+
+def tn_monomials(nvars: int, varorder: int) -> np.ndarray:
+    n = lib_tn().tbo_tn_monomials(nvars, varorder, None)
+    e = np.zeros((n, nvars), dtype=np.int32)
+    lib_tn().tbo_tn_monomials(nvars, varorder, _p(e))
+    return e
+
+
+def integrate_tn(tape: tb.Tape, order: int, nvars: int, varorder: int, q0, t0=0.0, tmax=None, params=None, *,
+                 trange=None, **kw):
+    """Jet-transport ensemble on the CPU oracle.  q0 [dof, ncoef, N]; returns dict(xfinal, tfinal, nsteps, status[, x_trange])."""
+    d, keep = tape.c_desc()
+    q = np.ascontiguousarray(q0, dtype=np.float64)
+    dof, nc, N = q.shape
+    per = 0
+    par = np.zeros(1)
+    if tape.npar:
+        par = np.ascontiguousarray(np.atleast_1d(np.asarray(params, dtype=np.float64)))
+        per = 1 if par.ndim == 2 else 0
+    o = _opts(**dict(kw, params_per_traj=per))
+    res = dict(xfinal=np.zeros((dof, nc, N)), tfinal=np.zeros(N), nsteps=np.zeros(N, dtype=np.int64),
+               status=np.zeros(N, dtype=np.int32))
+    tr = None
+    if trange is not None:
+        tr = np.ascontiguousarray(trange, dtype=np.float64)
+        res["x_trange"] = np.zeros((dof, nc, tr.size, N))
+        t0, tmax = tr[0], tr[-1]
+    rc = lib_tn().tbo_tn_integrate(C.byref(d), order, nvars, varorder, N, _p(q), _p(par), float(t0), float(tmax), _p(tr),
+                                   0 if tr is None else tr.size, C.byref(o), _p(res["xfinal"]), _p(res["tfinal"]),
+                                   _p(res["nsteps"]), _p(res["status"]), _p(res.get("x_trange")))
+    assert rc == 0, rc
+    del keep
+    return res
