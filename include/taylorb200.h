@@ -314,6 +314,17 @@ int tb_tn_monomials(const tb_tn_t *t, int32_t *expo);
 int tb_tn_integrate(tb_tn_t *t, int64_t N, const double *q0, const double *params, double t0, double tmax,
                     const double *trange, int64_t nt, const tb_opts_t *opts, const tb_tn_out_t *out);
 
+/* ---- large-state ODEs (one CTA per trajectory) -----------------------------------
+ * Same drivers (taylorinteg.jl:329-381, 582-642) for tapes too large for one thread:
+ * hundreds of components, 10^4 entries (spin_odes!, benchmark/manyspin_benchmarks.jl:10-41).
+ * Outputs: xfinal, tfinal, nsteps, status, xv_trange of the tb_out_t struct, HOST buffers.     */
+typedef struct tb_wide tb_wide_t;
+tb_wide_t *tb_wide_create(const tb_ode_t *ode, int order, int mode);
+void tb_wide_free(tb_wide_t *w);
+int tb_wide_info(const tb_wide_t *w, int *nops, int *nlev, int *nser, int *maxwidth);
+int tb_wide_integrate(tb_wide_t *w, int64_t N, const double *q0, const double *params, double t0, double tmax,
+                      const double *trange, int64_t nt, const tb_opts_t *opts, const tb_out_t *out);
+
 /* FP64 roofline probe: register-only DFMA chains on the current device.
  * Returns achieved TFLOP/s (2 flops per DFMA) over >= `seconds` of work.     */
 int tb_fp64_peak(double seconds, double *tflops, double *ms);

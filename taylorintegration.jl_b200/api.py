@@ -101,6 +101,56 @@ class Kernel:
         return xj, dt
 
 
+class WideKernel:
+    """Large-state program (one CTA per trajectory, csrc/tb_wide.cu): tapes with more than 16 components or more
+    than 200 entries, e.g. the many-spin system.  Plain drivers only (t0..tmax and trange)."""
+
+    def __init__(self, tape: Tape, order: int, mode: int = L.MODE_PARITY):
+        lib = L.lib()
+        self.tape, self.order, self.mode = tape, int(order), mode
+        desc, keep = tape.c_desc()
+        ode = lib.tb_ode_create(C.byref(desc))
+        if not ode:
+            raise L.TaylorB200Error("tb_ode_create: " + L.last_error())
+        self._w = lib.tb_wide_create(ode, self.order, mode)
+        err = L.last_error()
+        lib.tb_ode_free(ode)
+        del keep
+        if not self._w:
+            raise L.TaylorB200Error("tb_wide_create: " + err)
+
+    def __del__(self):
+        try:
+            if getattr(self, "_w", None):
+                L.lib().tb_wide_free(self._w)
+        except Exception:
+            pass
+
+    @property
+    def handle(self):
+        return self._w
+
+    def info(self) -> Dict[str, int]:
+        v = [C.c_int(-1) for _ in range(4)]
+        L.lib().tb_wide_info(self._w, *[C.byref(x) for x in v])
+        return dict(zip(["entries", "levels", "series", "max_width"], [x.value for x in v]))
+
+
+def is_wide(tape: Tape) -> bool:
+    return tape.dof > 16 or len(tape.ops) > 200
+
+
+_WIDE: Dict[Tuple, WideKernel] = {}
+
+
+def get_wide_kernel(tape: Tape, order: int, mode: int) -> WideKernel:
+    key = (id(tape), order, mode)
+    k = _WIDE.get(key)
+    if k is None:
+        k = _WIDE[key] = WideKernel(tape, order, mode)
+    return k
+
+
 _KERNELS: Dict[Tuple, Kernel] = {}
 _TAPES: Dict[Tuple, Tape] = {}
 
@@ -246,7 +296,17 @@ def _integrate(tape: Tape, kind: int, q0, t0, tmax, trange, order, abstol, param
         output = "steps" if single else "final"
     if output not in ("steps", "final"):
         raise ValueError("output must be 'steps' or 'final'")
-    k = get_kernel(tape, int(order), kind, _mode(mode), **(kernel_opts or {}))
+    kernel_opts = dict(kernel_opts or {})
+    wide = bool(kernel_opts.pop("wide", False)) or is_wide(tape)
+    if wide:
+        if kind != L.KIND_PLAIN:
+            raise L.TaylorB200Error("large-state tapes support the plain drivers only (no events / Lyapunov yet)")
+        if single and output == "steps" and trange is None:
+            raise L.TaylorB200Error("large-state tapes return final states or trange outputs; pass q0 as [dof, N] "
+                                    "or a trange")
+        k = get_wide_kernel(tape, int(order), _mode(mode))
+    else:
+        k = get_kernel(tape, int(order), kind, _mode(mode), **(kernel_opts or {}))
     cap = int(event_capacity) if event_capacity else int(maxsteps) + 1
     o = make_opts(abstol, reltol, minstepsize, maxstepsize, maxsteps, eventorder, newtoniter, nrabstol, cap, per)
     stride = int(maxsteps) + 1
@@ -264,8 +324,15 @@ def _integrate(tape: Tape, kind: int, q0, t0, tmax, trange, order, abstol, param
         assert tr.size >= 2 and (np.all(d > 0) or np.all(d < 0)), "trange must be sorted"  # taylorinteg.jl:489,573
         sol.x_trange = np.empty((dof, tr.size, N))
         out.xv_trange = sol.x_trange.ctypes.data_as(L._DP)
-        L.check(lib.tb_integrate_trange(k.handle, N, _ptr(q), _ptr(par), _ptr(tr), tr.size, C.byref(o), C.byref(out)),
-                "tb_integrate_trange")
+        if wide:
+            L.check(lib.tb_wide_integrate(k.handle, N, _ptr(q), _ptr(par), float(tr[0]), float(tr[-1]), _ptr(tr), tr.size,
+                                          C.byref(o), C.byref(out)), "tb_wide_integrate")
+        else:
+            L.check(lib.tb_integrate_trange(k.handle, N, _ptr(q), _ptr(par), _ptr(tr), tr.size, C.byref(o),
+                                            C.byref(out)), "tb_integrate_trange")
+    elif wide:
+        L.check(lib.tb_wide_integrate(k.handle, N, _ptr(q), _ptr(par), float(t0), float(tmax), None, 0, C.byref(o),
+                                      C.byref(out)), "tb_wide_integrate")
     else:
         if output == "steps":
             sol.t, sol.x = np.empty((stride, N)), np.empty((dof, stride, N))

@@ -88,3 +88,56 @@ def lorenz_ensemble(N: int):
 
 
 LORENZ = dict(order=28, abstol=1e-20, t0=0.0, tmax=100.0, maxsteps=20_000)
+
+
+# -- config 4: classical many-spin system, benchmark/manyspin_benchmarks.jl:10-96 --------------------------------
+def fix_J(nn: int, alpha: float = 1.4) -> np.ndarray:
+    """Long-range couplings J[i, i+d] = J[i+d, i] = 1/d^alpha (manyspin_benchmarks.jl:72-82)."""
+    J = np.zeros((nn, nn))
+    for d in range(1, nn):
+        val = 1.0 / d ** alpha
+        for i in range(nn - d):
+            J[i, i + d] = val
+            J[i + d, i] = val
+    return J
+
+
+def fix_B(nn: int, seed: int = 20261104) -> np.ndarray:
+    """Local fields.  The reference tabulates 20 values in [0.8, 1.2) (manyspin_benchmarks.jl:46-69) and asserts
+    nn < 21; for larger systems the same range is drawn from a seeded generator."""
+    return np.random.Generator(np.random.PCG64(seed)).uniform(0.8, 1.2, size=nn)
+
+
+def manyspin_tape(nn: int, B: np.ndarray = None, J: np.ndarray = None):
+    """`spin_odes!` (manyspin_benchmarks.jl:10-41) with `nn`, `B`, `J` as the `local` numbers they are there."""
+    B = fix_B(nn) if B is None else np.asarray(B, dtype=np.float64)
+    J = fix_J(nn) if J is None else np.asarray(J, dtype=np.float64)
+
+    def spin_odes(dq, q, p, t):
+        x = [q[3 * i] for i in range(nn)]
+        y = [q[3 * i + 1] for i in range(nn)]
+        z = [q[3 * i + 2] for i in range(nn)]
+        for i in range(nn):
+            sum_s = 0.0  # zero(x[1])
+            for a in range(nn):
+                xJ = float(J[a, i]) * x[a]
+                sum_s = sum_s + xJ
+            dq[3 * i] = float(-B[i]) * y[i]
+            dq[3 * i + 1] = float(B[i]) * x[i] + z[i] * sum_s
+            dq[3 * i + 2] = (-y[i]) * sum_s
+
+    return taylorize(spin_odes, 3 * nn, 0, name=f"spin_odes!({nn})")
+
+
+def manyspin_ensemble(nn: int, N: int, seed: int = 20261104) -> np.ndarray:
+    """Random spins on the unit sphere as in `ini_conditions!` (manyspin_benchmarks.jl:83-96); q0 [3 nn, N]."""
+    rng = np.random.Generator(np.random.PCG64(seed + 1))
+    sz = 2.0 * (rng.random((nn, N)) - 0.5)
+    pha = 2.0 * np.pi * rng.random((nn, N))
+    a = np.sqrt(1.0 - sz * sz)
+    q0 = np.empty((3 * nn, N))
+    q0[0::3], q0[1::3], q0[2::3] = a * np.cos(pha), a * np.sin(pha), sz
+    return q0
+
+
+MANYSPIN = dict(order=25, abstol=1e-20, t0=0.0, tmax=10.0, maxsteps=5000, nspin=100)
