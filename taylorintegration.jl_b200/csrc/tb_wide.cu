@@ -47,7 +47,7 @@ struct WOp {
     int para, parb; /* parameter index of a numeric operand, -1 = immediate */
     double imma, immb;
     double imm;     /* pow! exponent */
-    int lc_off, lc_n;
+    int lc_off, lc_n, lc_stride; /* term j of the chain at lc_off + j*lc_stride (chains of a level interleaved: coalesced) */
 };
 
 struct WArgs {
@@ -199,13 +199,14 @@ __device__ void exec_op(const WArgs &A, double *__restrict__ W, const double *pa
         case W_LINCOMB: { /* ((start + c1 x1[k]) + c2 x2[k]) + ... : the fused add!/mul! chain, in tape order */
             const double *cf = A.lc_coef + o.lc_off;
             const int *sr = A.lc_ser + o.lc_off;
+            const int ls = o.lc_stride;
             int j0 = 0;
             if (sa) { /* numeric start: add!(c, a::Number, b, k) touches k = 0 only */
-                const double m0 = WM(cf[0], W[(size_t)sr[0] * np1 + k]);
+                const double m0 = WM(__ldg(cf), W[(size_t)__ldg(sr) * np1 + k]);
                 r = k == 0 ? WA(na, m0) : m0;
                 j0 = 1;
             } else r = a[k];
-            for (int j = j0; j < o.lc_n; j++) r = mad<FAST>(cf[j], W[(size_t)sr[j] * np1 + k], r);
+            for (int j = j0; j < o.lc_n; j++) r = mad<FAST>(__ldg(cf + (size_t)j * ls), W[(size_t)__ldg(sr + (size_t)j * ls) * np1 + k], r);
             break;
         }
         default: break;
@@ -491,6 +492,31 @@ tb_wide_t *tb_wide_create(const tb_ode_t *ode, int order, int mode) {
     w->ops.resize(prog.size());
     std::vector<int> fill(w->lev_off.begin(), w->lev_off.end() - 1);
     for (size_t j = 0; j < prog.size(); j++) w->ops[fill[level[j]]++] = prog[j]; /* stable inside a level */
+    /* interleave the chains of one level: term j of the p-th chain at base + j*W + p, so the threads of a warp
+     * (consecutive entries of the level) read consecutive coefficients                                       */
+    std::vector<double> cT;
+    std::vector<int> sT;
+    for (int l = 0; l < nlev; l++) {
+        std::vector<int> chains;
+        int longest = 0;
+        for (int j = w->lev_off[l]; j < w->lev_off[l + 1]; j++)
+            if (w->ops[j].op == W_LINCOMB) { chains.push_back(j); longest = std::max(longest, w->ops[j].lc_n); }
+        const int Wd = (int)chains.size();
+        const size_t base = cT.size();
+        cT.resize(base + (size_t)Wd * longest, 0.0);
+        sT.resize(base + (size_t)Wd * longest, 0);
+        for (int pidx = 0; pidx < Wd; pidx++) {
+            WOp &o = w->ops[chains[pidx]];
+            for (int t = 0; t < o.lc_n; t++) {
+                cT[base + (size_t)t * Wd + pidx] = w->lc_coef[o.lc_off + t];
+                sT[base + (size_t)t * Wd + pidx] = w->lc_ser[o.lc_off + t];
+            }
+            o.lc_off = (int)(base + pidx);
+            o.lc_stride = Wd;
+        }
+    }
+    w->lc_coef.swap(cT);
+    w->lc_ser.swap(sT);
     return w;
 }
 
