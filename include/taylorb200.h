@@ -278,6 +278,9 @@ int tb_integrate_device(tb_kernel_t *k, int64_t N, const double *d_q0, const dou
                         const tb_opts_t *opts, const tb_out_t *d_out, void *d_work, void *stream);
 /* launches issued so far by this library (all kernels), for bench accounting */
 int64_t tb_launch_count(void);
+/* device time (CUDA events, ms) of the fused kernel launched by the last HOST-buffer entry point
+ * (tb_integrate*, tb_tn_integrate, tb_wide_integrate) called on this thread; -1 before any call */
+double tb_last_kernel_ms(void);
 
 /* First Taylor step of each trajectory: jets x[dof x (order+1) x N] (element
  * (c,k,i) at (c*(order+1)+k)*N + i) and the step size dt[N]. Host buffers.   */

@@ -696,7 +696,14 @@ struct UGen {
 
 int generate_unrolled(const Ode &ode, const tb_compile_opts_t &co, Layout &L, std::string &src, std::string &err) {
     const tb_ode_desc_t &d = ode.desc;
-    if (co.kind != TB_KIND_PLAIN) { err = "the unrolled generator covers TB_KIND_PLAIN"; return TB_ERR_UNSUPPORTED; }
+    /* events: supported when g is a state component (Poincare-section style, e.g. g = x[2] of
+     * test/rootfinding.jl:26) with an optional gate on another state component; event functions that need
+     * their own tape go to variant 1                                                                      */
+    const bool events = co.kind == TB_KIND_EVENTS;
+    if (events) {
+        const bool gate_ok = d.ev_gate_cmp == TB_GATE_ALWAYS || TB_OPERAND_KIND(d.ev_gate) == TB_K_X;
+        if (d.ev_nops != 0 || TB_OPERAND_KIND(d.ev_g) != TB_K_X || !gate_ok) { err = "the unrolled generator covers events on state components"; return TB_ERR_UNSUPPORTED; }
+    } else if (co.kind != TB_KIND_PLAIN) { err = "the unrolled generator covers TB_KIND_PLAIN and TB_KIND_EVENTS"; return TB_ERR_UNSUPPORTED; }
     if (co.order < 1 || co.order > 40) { err = "order must be in 1..40 for the unrolled generator"; return TB_ERR_UNSUPPORTED; }
     if (d.dof > 16 || d.nops > 200) { err = "tape too large to unroll"; return TB_ERR_UNSUPPORTED; }
     std::set<int32_t> seen;
@@ -721,6 +728,8 @@ int generate_unrolled(const Ode &ode, const tb_compile_opts_t &co, Layout &L, st
     L.nx = d.dof;
     L.nslot = g.nsm;
     L.slot.clear();
+    const int evslot = g.nsm; /* the series of g gets a shared-memory slot of its own (dynamic indexing in findroot!) */
+    if (events) g.nsm += 1;
     const size_t per_traj = (size_t)std::max(1, g.nsm) * np1 * sizeof(double);
     const size_t smem_max = 227 * 1024;
     int bt = co.block_threads;
@@ -760,6 +769,24 @@ int generate_unrolled(const Ode &ode, const tb_compile_opts_t &co, Layout &L, st
     e.line("};");
     g.emit_jets(e);
     g.emit_accessor(e);
+    if (events) {
+        const int cg = TB_OPERAND_INDEX(d.ev_g);
+        e.line("#define TB_EVSLOT %d", evslot);
+        e.line("#define TB_EV_G(kk) S(TB_EVSLOT, (kk))");
+        const char *cmp[] = {"", ">", "<", ">=", "<="};
+        if (d.ev_gate_cmp == TB_GATE_ALWAYS) e.line("#define TB_EV_GATE_EXPR true");
+        else e.line("#define TB_EV_GATE_EXPR (tb_u_x(J, smt, x0, %d, 0) %s 0.0)", TB_OPERAND_INDEX(d.ev_gate), cmp[d.ev_gate_cmp]);
+        e.line("/* coefficient k (run-time) of g = x[%d] */", cg);
+        e.line("__device__ __forceinline__ double tb_u_gcoef(const TbJets &J, const double *__restrict__ smt, const double *__restrict__ x0, const int k) {");
+        e.line("  switch (k) {");
+        for (int k = 0; k <= co.order; k++) e.line("    case %d: return tb_u_x(J, smt, x0, %d, %d);", k, cg, k);
+        e.line("    default: return 0.0;");
+        e.line("  }");
+        e.line("}");
+        e.line("__device__ __forceinline__ void tb_u_gcopy(const TbJets &J, double *__restrict__ smt, const double *__restrict__ x0) {");
+        for (int k = 0; k <= co.order; k++) e.line("  S(TB_EVSLOT, %d) = tb_u_x(J, smt, x0, %d, %d);", k, cg, k);
+        e.line("}");
+    }
     e.s += embedded_device_drv();
     if (!g.err.empty()) { err = g.err; return TB_ERR_ARG; }
     src.swap(e.s);

@@ -245,6 +245,7 @@ __device__ __forceinline__ void tb_eval_g_dg(const double *__restrict__ smt, int
     *gv = s;
     *dgv = ds;
 }
+#if TB_VARIANT == 1
 /* g(dx, x, params, t) on the current jets: returns the Bool of the tuple */
 __device__ __forceinline__ bool tb_eval_event(double *__restrict__ smt, const double *par, double t0) {
 #if TB_EV_NOPS > 0
@@ -254,6 +255,7 @@ __device__ __forceinline__ bool tb_eval_event(double *__restrict__ smt, const do
 #endif
     return TB_EV_GATE_EXPR;
 }
+#endif
 #endif
 
 /* ---- one trajectory ------------------------------------------------------- */
@@ -342,9 +344,19 @@ __device__ __forceinline__ bool tb_traj_init(TbTraj &T, double *__restrict__ smt
 #if TB_KIND == 1
     /* rootfinding.jl:377-378: g on the initial jets, which the parsed-method
      * probe (jetcoeffs.jl:181-182 via cache.jl:266) has already filled.       */
+#if TB_VARIANT == 1
     tb_jetcoeffs(smt, T.par, T.t0);
     T.f_old = tb_eval_event(smt, T.par, T.t0);
     T.g_old = TB_EV_G(a.eventorder);
+#else
+    { /* variant 2: g is a state component (generated accessors), jets in registers / shared memory */
+        TbJets J;
+        const double *x0 = T.x0;
+        tb_u_jets(J, smt, T.par, T.t0, x0);
+        T.f_old = TB_EV_GATE_EXPR;
+        T.g_old = tb_u_gcoef(J, smt, x0, a.eventorder);
+    }
+#endif
     T.dt = 0.0;
     T.dt_old = 0.0;
     T.nevents = 1;
@@ -449,17 +461,27 @@ __device__ __forceinline__ bool tb_traj_step(TbTraj &T, double *__restrict__ smt
 #elif TB_KIND == 1
     /* taylorinteg!(dense, f!, g, ...): src/rootfinding.jl:392-436; findroot! 176-235 */
     const int eo = a.eventorder;
+    TB_JETS_DECL
     T.dt_old = T.dt;
-    tb_jetcoeffs(smt, T.par, T.t0);
-    double dt = tb_stepsize(smt, a);
+    TB_COMPUTE_JETS(T);
+    double dt = TB_STEPSIZE(a);
     dt = M_(T.sign, fmin(dt, M_(T.sign, B_(T.tmax, T.t0))));
     T.dt = dt;
+    double xn[TB_DOF];
 #pragma unroll
-    for (int c = 0; c < TB_DOF; c++) T.x0[c] = tb_horner(smt, c, dt);
+    for (int c = 0; c < TB_DOF; c++) xn[c] = TB_HORNER(c, dt);
     tb_store_psol(T, TB_JETS_ARGS, a);
+#if TB_VARIANT == 1
     const bool f_now = tb_eval_event(smt, T.par, T.t0);
     const double g_now = TB_EV_G(eo);
+#else
+    const bool f_now = TB_EV_GATE_EXPR;
+    const double g_now = tb_u_gcoef(J, smt, x0, eo);
+#endif
     if (T.f_old && f_now && (M_(T.g_old, g_now) < 0.0)) { /* surfacecrossing: rootfinding.jl:124-132 */
+#if TB_VARIANT == 2
+        tb_u_gcopy(J, smt, x0); /* the series of g into its shared-memory slot: findroot! indexes it dynamically */
+#endif
         int nriter = 1;
         const double slope = D_(B_(g_now, T.g_old), T.dt_old);
         const double dt_li = N_(D_(g_now, slope));
@@ -474,14 +496,18 @@ __device__ __forceinline__ bool tb_traj_step(TbTraj &T, double *__restrict__ smt
         if (T.nevents <= a.event_cap) {
             const long long e = T.nevents - 1, N = a.N;
             if (a.tevents) a.tevents[e * N + T.i] = A_(T.t0, dt_nr);
-            if (a.xevents)
+            if (a.xevents) {
+                TB_UNROLL_V2
                 for (int c = 0; c < TB_DOF; c++)
-                    a.xevents[((long long)c * a.event_cap + e) * N + T.i] = tb_horner(smt, c, dt_nr);
+                    a.xevents[((long long)c * a.event_cap + e) * N + T.i] = TB_HORNER(c, dt_nr);
+            }
             if (a.gresids) a.gresids[e * N + T.i] = gv;
         } else
             T.st |= TB_ST_EVENT_OVERFLOW;
         T.nevents += 1;
     }
+#pragma unroll
+    for (int c = 0; c < TB_DOF; c++) T.x0[c] = xn[c];
     T.g_old = g_now;
     T.f_old = f_now;
     T.t0 = A_(T.t0, dt);

@@ -40,6 +40,7 @@ const char *embedded_device_pre();
 const char *embedded_device_drv();
 
 void set_error(const std::string &msg);
+void set_last_kernel_ms(double ms);
 
 } // namespace tb
 

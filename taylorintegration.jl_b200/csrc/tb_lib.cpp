@@ -29,6 +29,8 @@ static thread_local std::string g_err;
 void set_error(const std::string &m) { g_err = m; }
 static std::atomic<long long> g_launches{0};
 void count_launch(long long n) { g_launches += n; }
+static thread_local double g_last_ms = -1.0;
+void set_last_kernel_ms(double ms) { g_last_ms = ms; }
 
 /* ---- driver API, resolved lazily ------------------------------------------ */
 struct Driver {
@@ -396,10 +398,20 @@ static int integrate_host(tb_kernel *k, int64_t N, const double *q0, const doubl
             TB_CUDA(cudaMemsetAsync(*it.dptr, 0, it.bytes, st));
     TbArgs a;
     fill_args(a, N, d_q0, d_par, t0, tmax, d_tr, nt, *opts, dv, work);
+    cudaEvent_t e0, e1;
+    TB_CUDA(cudaEventCreate(&e0));
+    TB_CUDA(cudaEventCreate(&e1));
+    TB_CUDA(cudaEventRecord(e0, st));
     rc = launch(k, l, l->ensemble, a, true, st);
     if (rc) return rc;
+    TB_CUDA(cudaEventRecord(e1, st));
     for (auto &it : outs) TB_CUDA(cudaMemcpyAsync(it.host, *it.dptr, it.bytes, cudaMemcpyDeviceToHost, st));
     TB_CUDA(cudaStreamSynchronize(st));
+    float ms = -1.f;
+    cudaEventElapsedTime(&ms, e0, e1);
+    set_last_kernel_ms(ms);
+    cudaEventDestroy(e0);
+    cudaEventDestroy(e1);
     return TB_OK;
 }
 
@@ -557,6 +569,7 @@ int tb_integrate_device(tb_kernel_t *k, int64_t N, const double *d_q0, const dou
 }
 
 int64_t tb_launch_count(void) { return g_launches.load(); }
+double tb_last_kernel_ms(void) { return g_last_ms; }
 
 int tb_jet(tb_kernel_t *k, int64_t N, const double *q0, const double *params, double t0, const tb_opts_t *opts,
            double *xjet, double *dt) {

@@ -25,6 +25,7 @@
 
 namespace tb {
 void count_launch(long long n);
+void set_last_kernel_ms(double ms);
 }
 struct tb_ode {
     tb::Ode o;
@@ -535,11 +536,21 @@ int tb_tn_integrate(tb_tn_t *t, int64_t N, const double *q0, const double *param
         a.nsteps = dns; a.status = dst; a.xv_trange = dxv; a.counter = dctr;
     }
     if (rc == TB_OK) {
+        cudaEvent_t e0, e1;
+        cudaEventCreate(&e0);
+        cudaEventCreate(&e1);
+        cudaEventRecord(e0, 0);
         if (fast) tn_kernel<true><<<(unsigned)blocks, threads, smem>>>(a);
         else tn_kernel<false><<<(unsigned)blocks, threads, smem>>>(a);
+        cudaEventRecord(e1, 0);
         tb::count_launch(1);
         fail(cudaGetLastError(), "tn_kernel launch");
         fail(cudaDeviceSynchronize(), "tn_kernel");
+        float ms = -1.f;
+        cudaEventElapsedTime(&ms, e0, e1);
+        tb::set_last_kernel_ms(ms);
+        cudaEventDestroy(e0);
+        cudaEventDestroy(e1);
     }
     if (rc == TB_OK) {
         if (out->xfinal) fail(cudaMemcpy(out->xfinal, dxf, 8 * nq, cudaMemcpyDeviceToHost), "copy xfinal");

@@ -23,6 +23,7 @@
 
 namespace tb {
 void count_launch(long long n);
+void set_last_kernel_ms(double ms);
 }
 struct tb_ode {
     tb::Ode o;
@@ -601,11 +602,21 @@ int tb_wide_integrate(tb_wide_t *w, int64_t N, const double *q0, const double *p
         a.nsteps = dns; a.status = dst; a.xv_trange = dxv; a.counter = dctr;
     }
     if (rc == TB_OK) {
+        cudaEvent_t e0, e1;
+        cudaEventCreate(&e0);
+        cudaEventCreate(&e1);
+        cudaEventRecord(e0, 0);
         if (fast) wide_kernel<true><<<(unsigned)blocks, threads>>>(a);
         else wide_kernel<false><<<(unsigned)blocks, threads>>>(a);
+        cudaEventRecord(e1, 0);
         tb::count_launch(1);
         fail(cudaGetLastError(), "wide_kernel launch");
         fail(cudaDeviceSynchronize(), "wide_kernel");
+        float ms = -1.f;
+        cudaEventElapsedTime(&ms, e0, e1);
+        tb::set_last_kernel_ms(ms);
+        cudaEventDestroy(e0);
+        cudaEventDestroy(e1);
     }
     if (rc == TB_OK) {
         if (out->xfinal) fail(cudaMemcpy(out->xfinal, dxf, 8 * nq, cudaMemcpyDeviceToHost), "copy xfinal");

@@ -1,7 +1,7 @@
 #!/usr/bin/env python3
 """Throughput of BASELINE.json configs 2-5 through the public host-buffer API (one JSON line each).
-Config 1 (the headline) is bench.py.  Timing: wall clock around the API call after one warm-up call (the call
-includes H2D of inputs, the single fused launch, and D2H of results).  Flop models: SURVEY.md section 8(d).
+Config 1 (the headline) is bench.py.  Timing: device time of the single fused launch (CUDA events inside the library, tb_last_kernel_ms) after one
+warm-up call; the wall clock of the whole host-buffer call (H2D, launch, D2H from pageable memory) is reported beside it.  Flop models: SURVEY.md section 8(d).
 
     python tools/bench_configs.py [pendulum] [lorenz] [manyspin] [jet2] [jet4] [--scale S]
 """
@@ -28,17 +28,23 @@ mode = "fast" if "--fast" in sys.argv else "parity"
 peak_tf, _ = tb.fp64_peak(0.3)
 
 
+WALL = []
+
+
 def timed(fn):
     fn()  # warm-up (NVRTC compile, module load, allocations)
     t0 = time.perf_counter()
     r = fn()
-    return r, time.perf_counter() - t0
+    wall = time.perf_counter() - t0
+    ms = tb._lib.lib().tb_last_kernel_ms()
+    WALL.append(wall)
+    return r, (ms * 1e-3 if ms > 0 else wall)
 
 
 def report(name, workload, steps, secs, flops_per_step, ok, extra=None):
     ach = steps * flops_per_step / secs / 1e12
     line = {"config": name, "workload": workload, "mode": mode, "value": steps / secs, "unit": "trajectory-steps/s",
-            "seconds": secs, "trajectory_steps": int(steps), "flops_per_step": flops_per_step,
+            "kernel_seconds": secs, "api_wall_seconds": WALL[-1], "trajectory_steps": int(steps), "flops_per_step": flops_per_step,
             "roofline": {"bound": "fp64", "achieved": ach, "peak": peak_tf, "unit": "TFLOP/s", "frac": ach / peak_tf},
             "all_ok": bool(ok)}
     if extra:
