@@ -10,7 +10,10 @@ from .api import (EnsembleSolution, Kernel, TaylorSolution, fp64_peak, get_kerne
                   taylorinteg, taylorinteg_events)
 from .jettransport import JetSolution, JetTransport, taylorinteg_jet  # noqa: F401
 from . import problems  # noqa: F401
+from . import sharding  # noqa: F401
+from .sharding import lyap_taylorinteg_sharded, taylorinteg_sharded  # noqa: F401
 
 __all__ = ["taylorinteg", "lyap_taylorinteg", "taylorize", "TaylorSolution", "EnsembleSolution", "Kernel", "Tape",
            "sin", "cos", "sqrt", "exp", "log", "zero", "fp64_peak", "problems", "TaylorB200Error",
-           "JetTransport", "JetSolution", "taylorinteg_jet"]
+           "JetTransport", "JetSolution", "taylorinteg_jet", "sharding", "taylorinteg_sharded",
+           "lyap_taylorinteg_sharded"]
