@@ -627,7 +627,7 @@ struct UGen {
                     }
                     if (!grouping) break;
                 }
-                if ((co.flags & 128) && kmin != last_sync_k) { e.line("  TB_ORDER_SYNC();"); last_sync_k = kmin; }
+                if ((co.flags & 128) && kmin != last_sync_k && (!(co.flags & 2048) || kmin % 4 == 1)) { e.line("  TB_ORDER_SYNC();"); last_sync_k = kmin; }
                 e.line("  /* ---- order %d: %d recurrence chain group ---- */", kmin, (int)g.size());
                 emit_group(e, g);
                 if (!(co.flags & 8)) e.line("  asm volatile(\"\" ::: \"memory\");");
@@ -759,7 +759,7 @@ int generate_unrolled(const Ode &ode, const tb_compile_opts_t &co, Layout &L, st
     e.line("#define TB_KIND %d", co.kind);
     e.line("#define TB_EV_NOPS 0");
     e.line("#define TB_JAC_NOPS 0");
-    e.line("#define TB_BAR %d", (co.flags & 128) ? 1 : 0);
+    e.line("#define TB_BAR %d", (co.flags & 128) ? 1 : (co.flags & 1024) ? 2 : 0);
     e.s += embedded_math_h();
     e.s += embedded_device_pre();
     e.line("/* placement: %d series in registers, %d in shared memory */", g.nreg, g.nsm);

@@ -627,7 +627,13 @@ extern "C" __global__ void __launch_bounds__(TB_BT, TB_MINB) tb_ensemble_kernel(
         /* block lockstep: every warp runs every step until the whole block is out of work, so the
          * barriers inside the jet code are uniform and the warps share one instruction stream  */
         if (!__syncthreads_or(have || (a.lockstep && more))) break;
+#if TB_BAR == 2
+        /* step lockstep: one barrier per step only; the warps start every step together and drift by
+         * less than the instruction cache holds, so a line fetched by the leader serves the others */
+        if (have) { if (tb_traj_step(T, smt, a, true)) { tb_traj_finish(T, a); have = false; } }
+#else
         if (tb_traj_step(T, smt, a, have)) { tb_traj_finish(T, a); have = false; }
+#endif
 #else
         if (!__any_sync(full, have)) { if (!(a.lockstep && more)) break; else continue; }
         if (have) {

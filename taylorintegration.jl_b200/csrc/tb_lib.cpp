@@ -14,6 +14,9 @@
 #include <cuda_runtime.h>
 #include <dlfcn.h>
 #include <nvrtc.h>
+#include <dlfcn.h>
+#include <sys/stat.h>
+#include <unistd.h>
 
 #include <atomic>
 #include <cmath>
@@ -462,6 +465,48 @@ void tb_compile_opts_default(tb_compile_opts_t *o) {
     o->kind = TB_KIND_PLAIN;
 }
 
+static bool read_file(const std::string &path, std::vector<char> &out) {
+    FILE *f = fopen(path.c_str(), "rb");
+    if (!f) return false;
+    fseek(f, 0, SEEK_END);
+    long n = ftell(f);
+    fseek(f, 0, SEEK_SET);
+    out.resize(n > 0 ? (size_t)n : 0);
+    const bool ok = n >= 0 && (n == 0 || fread(out.data(), 1, (size_t)n, f) == (size_t)n);
+    fclose(f);
+    return ok;
+}
+static void write_file(const std::string &path, const void *p, size_t n) {
+    const std::string tmp = path + ".tmp" + std::to_string((long)getpid());
+    FILE *f = fopen(tmp.c_str(), "wb");
+    if (!f) return;
+    const bool ok = fwrite(p, 1, n, f) == n;
+    fclose(f);
+    if (ok) rename(tmp.c_str(), path.c_str()); else remove(tmp.c_str());
+}
+static std::string cache_path(const std::string &source, int mode) {
+    std::string dir;
+    if (const char *e = getenv("TB_CACHE_DIR")) dir = e;
+    else {
+        Dl_info di;
+        if (!dladdr((const void *)&tb_abi_version, &di) || !di.dli_fname) return std::string();
+        dir = di.dli_fname;
+        const size_t sl = dir.find_last_of('/');
+        dir = (sl == std::string::npos ? std::string(".") : dir.substr(0, sl)) + "/kcache";
+    }
+    mkdir(dir.c_str(), 0755);
+    unsigned long long h = 1469598103934665603ull;
+    auto mix = [&](const char *p, size_t n) { for (size_t i = 0; i < n; i++) { h ^= (unsigned char)p[i]; h *= 1099511628211ull; } };
+    mix(source.data(), source.size());
+    /* the NVRTC version is NOT part of the key: a process that imported torch first resolves libnvrtc.so.12 to
+     * torch's bundled 12.8, whose ptxas spills where 12.9 does not; cubins prebuilt by build() (CUDA 12.9) win */
+    const std::string tag = "|sm_100a|mode" + std::to_string(mode);
+    mix(tag.data(), tag.size());
+    char name[64];
+    snprintf(name, sizeof name, "/%016llx", h);
+    return dir + name;
+}
+
 const char *tb_generate_source(const tb_ode_t *ode, const tb_compile_opts_t *co) {
     static thread_local std::string src;
     if (!ode || !co) { set_error("tb_generate_source: NULL argument"); return nullptr; }
@@ -483,6 +528,15 @@ tb_kernel_t *tb_compile(const tb_ode_t *ode, const tb_compile_opts_t *co) {
         set_error("tb_compile: " + err);
         delete k;
         return nullptr;
+    }
+    /* on-disk cubin cache (in-tree, next to the library, so build() on the CPU box pre-compiles for the GPU box):
+     * key = FNV-1a of the generated source + compile mode.  TB_CF_NO_DISK_CACHE skips it. */
+    const std::string cpath = (k->co.flags & TB_CF_NO_DISK_CACHE) ? std::string() : cache_path(k->source, k->co.mode);
+    if (!cpath.empty() && read_file(cpath + ".cubin", k->cubin) && !k->cubin.empty()) {
+        std::vector<char> lg;
+        if (read_file(cpath + ".log", lg)) k->log.assign(lg.begin(), lg.end());
+        parse_ptxas(k->log, &k->regs, &k->local_bytes);
+        return k;
     }
     nvrtcProgram prog;
     if (nvrtcCreateProgram(&prog, k->source.c_str(), "tb_kernel.cu", 0, nullptr, nullptr) != NVRTC_SUCCESS) {
@@ -512,6 +566,13 @@ tb_kernel_t *tb_compile(const tb_ode_t *ode, const tb_compile_opts_t *co) {
     nvrtcGetCUBIN(prog, k->cubin.data());
     nvrtcDestroyProgram(&prog);
     parse_ptxas(k->log, &k->regs, &k->local_bytes);
+    if (!cpath.empty()) {
+        write_file(cpath + ".cubin", k->cubin.data(), k->cubin.size());
+        int maj = 0, min = 0;
+        nvrtcVersion(&maj, &min);
+        k->log += "\n[libtaylorb200] compiled by NVRTC " + std::to_string(maj) + "." + std::to_string(min) + "\n";
+        write_file(cpath + ".log", k->log.data(), k->log.size());
+    }
     return k;
 }
 
