@@ -191,6 +191,7 @@ typedef struct tb_compile_opts {
 #define TB_CF_DERIVE_X 512    /* parity mode: derive unread state jets from dx (default: stored) */
 #define TB_CF_BLOCK_LOCKSTEP 128 /* barrier per order: the warps of a block share one instruction stream */
 #define TB_CF_STEP_LOCKSTEP 1024 /* one block barrier per step (no barriers inside the jet body) */
+#define TB_CF_NO_TRIM_X 4096    /* parity mode: store x[0..2] of tail-only state jets as well */
 #define TB_CF_SYNC_EVERY4 2048   /* with TB_CF_BLOCK_LOCKSTEP: barrier every 4th order only */
 
 /* ---- integration options: keyword arguments of taylorinteg -------------- */

@@ -73,6 +73,9 @@ struct SeriesInfo {
     int id = -1;     /* register array index or shared-memory slot */
     double reads = 0; /* Cauchy-sum reads per step (placement weight) */
     int len = 0;      /* coefficients kept */
+    int base = 0;     /* shared memory: coefficient k lives at double (base + k) of the thread's column */
+    int trim = 0;     /* shared memory: coefficients 0..trim-1 are not stored (exactly recoverable, see analyse) */
+    int32_t dx = 0;   /* trimmed state jet: its derivative series */
 };
 
 struct UGen {
@@ -94,6 +97,8 @@ struct UGen {
         ser[o].reads += w;
     }
     bool derive_x = true;
+    bool trim_x = false;  /* parity: do not store x[0], x[1], x[2] of state jets that only Horner / stepsize read */
+    int smem_doubles = 0; /* shared-memory doubles per trajectory */
     void analyse(int reg_budget) {
         const tb_ode_desc_t &d = ode.desc;
         const double w = 0.5 * P * P;
@@ -136,7 +141,31 @@ struct UGen {
             if (si.reads > 0 && used + si.len <= reg_budget) { si.place = PL_REG; si.id = nreg++; used += si.len; }
             else { si.place = PL_SMEM; si.id = nsm++; }
         }
+        /* trimmed state jets: x[0] is the state itself, x[1] = dx[0]/1 and x[2] = dx[1]/2 are exact scalings of
+         * stored dx coefficients, so a state jet that no recurrence reads keeps only x[3..P] in shared memory.
+         * For Kepler-28 that is what lets 256 instead of 224 trajectories share one SM.                       */
+        if (trim_x && P >= 3)
+            for (int c = 0; c < d.dof; c++) {
+                int32_t x = TB_OPERAND(TB_K_X, c), dx = TB_OPERAND(TB_K_DX, c);
+                SeriesInfo &si = ser[x];
+                if (si.place != PL_SMEM || si.reads > 0 || !ser.count(dx) || ser[dx].place == PL_NONE || ser[dx].place == PL_DERIVED) continue;
+                if (ser[dx].reads <= 0) continue;
+                si.trim = 3;
+                si.dx = dx;
+            }
+        /* shared-memory layout: untrimmed series first (slot * (P+1), as S(slot, k)), trimmed ones packed after */
+        int run = 0;
+        for (int pass = 0; pass < 2; pass++)
+            for (auto &kv : ser) {
+                SeriesInfo &si = kv.second;
+                if (si.place != PL_SMEM || (si.trim != 0) != (pass == 1)) continue;
+                si.base = run - si.trim;
+                run += si.len - si.trim;
+            }
+        smem_doubles = run;
     }
+    std::string sref(const SeriesInfo &si, const std::string &k) const { return fmt("SB(%d, %s)", si.base, k.c_str()); }
+    std::string sref(const SeriesInfo &si, int k) const { return fmt("SB(%d, %d)", si.base, k); }
 
     /* ---- values ---------------------------------------------------------------
      * A coefficient (series o, index idx) is referred to by the NAME of the local
@@ -172,7 +201,8 @@ struct UGen {
         auto lt = loaded.find(Key(r.o, r.idx));
         if (lt != loaded.end()) return lt->second;
         std::string n = fmt("l%d", tmpc++);
-        e.line("  const double %s = S(%d, %d);", n.c_str(), it->second.id, r.idx);
+        if (r.idx < it->second.trim) { err = "internal: trimmed coefficient read by a recurrence"; return "0.0"; }
+        e.line("  const double %s = %s;", n.c_str(), sref(it->second, r.idx).c_str());
         loaded[Key(r.o, r.idx)] = n;
         return n;
     }
@@ -554,7 +584,7 @@ struct UGen {
         auto it = ser.find(o);
         if (it == ser.end()) return;
         if (it->second.place == PL_REG) e.line("  J.r%d[%d] = %s;", it->second.id, k, v.c_str());
-        else if (it->second.place == PL_SMEM) e.line("  S(%d, %d) = %s;", it->second.id, k, v.c_str());
+        else if (it->second.place == PL_SMEM && k >= it->second.trim) e.line("  %s = %s;", sref(it->second, k).c_str(), v.c_str());
     }
 
 
@@ -678,10 +708,16 @@ struct UGen {
         for (int c = 0; c < d.dof; c++) {
             const SeriesInfo &si = ser[TB_OPERAND(TB_K_X, c)];
             if (si.place == PL_REG) e.line("    case %d: return J.r%d[k];", c, si.id);
-            else if (si.place == PL_SMEM) e.line("    case %d: return S(%d, k);", c, si.id);
-            else {
+            else if (si.place == PL_SMEM && si.trim == 0) e.line("    case %d: return %s;", c, sref(si, "k").c_str());
+            else if (si.place == PL_SMEM) {
+                const SeriesInfo &di = ser[si.dx];
+                std::string r0 = di.place == PL_REG ? fmt("J.r%d[0]", di.id) : sref(di, 0);
+                std::string r1 = di.place == PL_REG ? fmt("J.r%d[1]", di.id) : sref(di, 1);
+                e.line("    case %d: return k == 0 ? x0[%d] : (k == 1 ? M_(%s, 1.0) : (k == 2 ? M_(%s, 0.5) : %s));", c, c, r0.c_str(),
+                       r1.c_str(), sref(si, "k").c_str());
+            } else {
                 const SeriesInfo &di = ser[TB_OPERAND(TB_K_DX, c)];
-                std::string ref = di.place == PL_REG ? fmt("J.r%d[k - 1]", di.id) : fmt("S(%d, k - 1)", di.id);
+                std::string ref = di.place == PL_REG ? fmt("J.r%d[k - 1]", di.id) : sref(di, "k - 1");
                 if (fast) e.line("    case %d: return k == 0 ? x0[%d] : %s * (1.0 / (double)k);", c, c, ref.c_str());
                 else e.line("    case %d: return k == 0 ? x0[%d] : tb_divc(%s, k);", c, c, ref.c_str());
             }
@@ -723,14 +759,15 @@ int generate_unrolled(const Ode &ode, const tb_compile_opts_t &co, Layout &L, st
     int budget = co.reg_budget > 0 ? co.reg_budget : (parity ? 4 : 3) * np1;
     if (co.reg_budget < 0) budget = 0;
     g.derive_x = parity ? (co.flags & 512) != 0 : !(co.flags & 256);
+    g.trim_x = parity && co.kind == TB_KIND_PLAIN && !(co.flags & 4096);
     g.analyse(budget);
     L.variant = 2;
     L.nx = d.dof;
     L.nslot = g.nsm;
     L.slot.clear();
     const int evslot = g.nsm; /* the series of g gets a shared-memory slot of its own (dynamic indexing in findroot!) */
-    if (events) g.nsm += 1;
-    const size_t per_traj = (size_t)std::max(1, g.nsm) * np1 * sizeof(double);
+    if (events) { g.nsm += 1; g.smem_doubles += np1; } /* trim_x is off for events: the slots are whole, S(TB_EVSLOT, k) is valid */
+    const size_t per_traj = (size_t)std::max(1, g.smem_doubles) * sizeof(double);
     const size_t smem_max = 227 * 1024;
     int bt = co.block_threads;
     if (bt <= 0) {
