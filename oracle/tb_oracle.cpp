@@ -687,6 +687,7 @@ extern "C" {
 
 /* accuracy probes for tests/test_math.py */
 double tbo_math_pow(double x, double y) { return tb_pow(x, y); }
+void tbo_math_pow_pair(double x1, double y1, double x2, double y2, double *r) { tb_pair p = tb_pow_pair(x1, y1, x2, y2); r[0] = p.a; r[1] = p.b; }
 double tbo_math_exp(double x) { return tb_exp(x); }
 double tbo_math_log(double x) { return tb_log(x); }
 void tbo_math_sincos(double x, double *s, double *c) { tb_sincos(x, s, c); }

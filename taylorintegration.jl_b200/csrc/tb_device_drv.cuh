@@ -28,6 +28,9 @@ __device__ __noinline__ double tb_stepsize_k(double a, double eps, int k) {
     return tb_pow(aux, kinv);
 }
 
+/* NOTE (round 1, measured): evaluating the two step-size powers in one interleaved body (tb_pow_pair, tb_math.h)
+ * costs 7 % on Kepler-28: the jets occupy ~232 registers across the call, and the wider callee spills. */
+
 #if TB_VARIANT == 1
 /* evaluate(a::Taylor1, dt): Horner, s = a[P]; s = s*dt + a[k]  (TaylorSeries) */
 __device__ __forceinline__ double tb_horner(const double *__restrict__ smt, int slot, double dt) {

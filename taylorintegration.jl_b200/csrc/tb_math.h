@@ -109,14 +109,18 @@ TB_HD double tb_pow2i(int k) { return TB_FROM_BITS(((unsigned long long)(k + 102
  * s, z and the first two series terms are carried in double-double, the tail
  * (1/7 ... 1/29) in double.  Relative error of the pair ~ 2^-66.
  * Domain: finite x > 0 (callers handle the rest).                            */
+TB_HD tb_dd tb_log_dd_norm(double x, int e);
 TB_HD tb_dd tb_log_dd(double x) {
     int e = 0;
-    unsigned long long u = TB_TO_BITS(x);
-    if ((u >> 52) == 0ull) { /* subnormal */
+    if ((TB_TO_BITS(x) >> 52) == 0ull) { /* subnormal */
         x = TB_MUL(x, 18014398509481984.0); /* 2^54 */
-        u = TB_TO_BITS(x);
         e = -54;
     }
+    return tb_log_dd_norm(x, e);
+}
+/* the branch-free body: x normal, positive, finite; result log(x) + e*ln2 */
+TB_HD tb_dd tb_log_dd_norm(double x, int e) {
+    unsigned long long u = TB_TO_BITS(x);
     e += (int)((u >> 52) & 0x7FFull) - 1023;
     double m = TB_FROM_BITS((u & 0x000FFFFFFFFFFFFFull) | 0x3FF0000000000000ull); /* [1,2) */
     if (m > 1.4142135623730951) { m = TB_MUL(m, 0.5); e += 1; }
@@ -167,10 +171,15 @@ TB_HD tb_dd tb_log_dd(double x) {
 }
 
 /* exp(h + l), |l| << |h|, result rounded to double; error < 0.6 ulp.         */
+TB_HD double tb_exp_dd_core(double h, double l);
 TB_HD double tb_exp_dd(double h, double l) {
     if (h != h) return h;
     if (h > 709.782712893384) return TB_FROM_BITS(0x7FF0000000000000ull);
     if (h < -745.2) return 0.0;
+    return tb_exp_dd_core(h, l);
+}
+/* the branch-free body: -745.2 <= h <= 709.78 */
+TB_HD double tb_exp_dd_core(double h, double l) {
     /* k = round(h / ln2) by the magic-number trick */
     double fn = TB_SUB(TB_FMA(h, 1.4426950408889634, 6755399441055744.0), 6755399441055744.0);
     int k = (int)fn;
@@ -234,6 +243,32 @@ TB_HD double tb_pow(double x, double y) {
     tb_dd p = tb_two_prod(y, L.hi);
     p.lo = TB_FMA(y, L.lo, p.lo);
     return TB_MUL(sgn, tb_exp_dd(p.hi, p.lo));
+}
+
+/* Two independent powers x1^y1, x2^y2 in one straight-line body, so that the two dependent
+ * chains interleave on the FP64 pipe (8-cycle dependent-issue latency on B200; the step-size
+ * control calls pow twice per step, stepsize.jl:83-86).  Same operations as tb_pow, same bits;
+ * anything outside the plain case (x normal, positive, finite; moderate result) goes to tb_pow. */
+typedef struct { double a, b; } tb_pair;
+TB_HD tb_pair tb_pow_pair(double x1, double y1, double x2, double y2) {
+    tb_pair r;
+    const unsigned long long e1 = (TB_TO_BITS(x1) >> 52), e2 = (TB_TO_BITS(x2) >> 52); /* sign + exponent fields */
+    const int plain = e1 >= 1ull && e1 <= 0x7FEull && e2 >= 1ull && e2 <= 0x7FEull && x1 != 1.0 && x2 != 1.0 &&
+                      y1 == y1 && y2 == y2 && y1 != 0.0 && y2 != 0.0;
+    if (plain) {
+        tb_dd L1 = tb_log_dd_norm(x1, 0), L2 = tb_log_dd_norm(x2, 0);
+        tb_dd p1 = tb_two_prod(y1, L1.hi), p2 = tb_two_prod(y2, L2.hi);
+        p1.lo = TB_FMA(y1, L1.lo, p1.lo);
+        p2.lo = TB_FMA(y2, L2.lo, p2.lo);
+        if (TB_ABS(p1.hi) < 700.0 && TB_ABS(p2.hi) < 700.0) {
+            r.a = TB_MUL(1.0, tb_exp_dd_core(p1.hi, p1.lo));
+            r.b = TB_MUL(1.0, tb_exp_dd_core(p2.hi, p2.lo));
+            return r;
+        }
+    }
+    r.a = tb_pow(x1, y1);
+    r.b = tb_pow(x2, y2);
+    return r;
 }
 
 /* ---- sin / cos --------------------------------------------------------------

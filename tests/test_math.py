@@ -46,3 +46,18 @@ def test_pow_exp_log_ulp():
     for x in 10 ** rng.uniform(-300, 300, 3000):
         m = max(m, _ulp_err(o.tbo_math_log(float(x)), mp.log(mp.mpf(float(x)))))
     assert m < 0.6, m
+
+
+def test_pow_pair_is_bitwise_tb_pow():
+    # tb_pow_pair (the interleaved step-size pair of the parity kernel) must return tb_pow's bits, special cases included
+    o = oracle.lib()
+    o.tbo_math_pow_pair.argtypes = [C.c_double] * 4 + [C.c_void_p]
+    rng = np.random.default_rng(3)
+    xs = list(10 ** rng.uniform(-320, 308, 4000)) + [0.0, 1.0, -2.0, np.inf, np.nan, 5e-324, 2.2250738585072014e-308, 1e-310]
+    r = (C.c_double * 2)()
+    for i, x1 in enumerate(xs):
+        x2 = xs[(i * 7 + 3) % len(xs)]
+        for y1, y2 in ((1 / 27, 1 / 28), (1 / 24, 1 / 25), (300.0, -300.0), (0.0, 1.5)):
+            o.tbo_math_pow_pair(float(x1), y1, float(x2), y2, r)
+            e1, e2 = o.tbo_math_pow(float(x1), y1), o.tbo_math_pow(float(x2), y2)
+            assert np.array_equal(np.array([r[0], r[1]]).view(np.uint64), np.array([e1, e2]).view(np.uint64)), (x1, y1, x2, y2)
