@@ -166,7 +166,12 @@ enum tb_mode {
 enum tb_kind {
     TB_KIND_PLAIN = 0,  /* taylorinteg (t0,tmax) and trange                   */
     TB_KIND_EVENTS = 1, /* + findroot!                                        */
-    TB_KIND_LYAP = 2    /* lyap_taylorinteg                                   */
+    TB_KIND_LYAP = 2,   /* lyap_taylorinteg                                   */
+    TB_KIND_LYAPCOL = 3 /* lyap_taylorinteg, column-parallel: the ODE handed to tb_compile is the COLUMN SYSTEM
+                         * [x; v] of 2*n components (x' = f(x), v' = J(x) v, built by the front end from the tape
+                         * and its Jacobian); a team of n lanes integrates one trajectory, lane j carrying column j
+                         * of the fundamental matrix, and the per-step modified Gram-Schmidt runs over warp
+                         * shuffles.  q0, xfinal, lambda are [n x N] as for TB_KIND_LYAP; same bits.            */
 };
 
 typedef struct tb_compile_opts {

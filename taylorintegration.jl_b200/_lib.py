@@ -29,7 +29,7 @@ K_NONE, K_X, K_DX, K_TMP, K_PAR, K_TIME, K_IMM = range(7)
 JAC_ZERO, JAC_CONST, JAC_SERIES, JAC_PAR = range(4)
 GATE_ALWAYS, GATE_GT0, GATE_LT0, GATE_GE0, GATE_LE0 = range(5)
 MODE_PARITY, MODE_FAST = 0, 1
-KIND_PLAIN, KIND_EVENTS, KIND_LYAP = 0, 1, 2
+KIND_PLAIN, KIND_EVENTS, KIND_LYAP, KIND_LYAPCOL = 0, 1, 2, 3
 
 
 def operand(kind: int, index: int = 0) -> int:

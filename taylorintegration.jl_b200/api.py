@@ -23,7 +23,7 @@ from typing import Callable, Dict, Optional, Tuple, Union
 import numpy as np
 
 from . import _lib as L
-from .tape import Tape, taylorize
+from .tape import Tape, lyap_column_tape, taylorize
 
 _EPS = float(np.finfo(np.float64).eps)
 
@@ -153,6 +153,16 @@ def get_wide_kernel(tape: Tape, order: int, mode: int) -> WideKernel:
 
 _KERNELS: Dict[Tuple, Kernel] = {}
 _TAPES: Dict[Tuple, Tape] = {}
+
+
+_COLUMN_TAPES: Dict[int, Tuple[Tape, Optional[Tape]]] = {}
+
+
+def _column_tape(tape: Tape) -> Optional[Tape]:
+    ent = _COLUMN_TAPES.get(id(tape))
+    if ent is None or ent[0] is not tape:
+        ent = _COLUMN_TAPES[id(tape)] = (tape, lyap_column_tape(tape))
+    return ent[1]
 
 
 def get_kernel(tape: Tape, order: int, kind: int, mode: int, **kw) -> Kernel:
@@ -306,7 +316,15 @@ def _integrate(tape: Tape, kind: int, q0, t0, tmax, trange, order, abstol, param
                                     "or a trange")
         k = get_wide_kernel(tape, int(order), _mode(mode))
     else:
-        k = get_kernel(tape, int(order), kind, _mode(mode), **(kernel_opts or {}))
+        ktape, kkind = tape, kind
+        columns = kernel_opts.pop("columns", True)
+        if kind == L.KIND_LYAP and columns:
+            # column-parallel Lyapunov kernel (a team of dof lanes per trajectory, TB_KIND_LYAPCOL) when the
+            # Jacobian can be written as a column tape with the same bits; else the single-thread kernel
+            col = _column_tape(tape)
+            if col is not None:
+                ktape, kkind = col, L.KIND_LYAPCOL
+        k = get_kernel(ktape, int(order), kkind, _mode(mode), **(kernel_opts or {}))
     cap = int(event_capacity) if event_capacity else int(maxsteps) + 1
     o = make_opts(abstol, reltol, minstepsize, maxstepsize, maxsteps, eventorder, newtoniter, nrabstol, cap, per)
     stride = int(maxsteps) + 1

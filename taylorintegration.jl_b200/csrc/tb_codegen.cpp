@@ -350,6 +350,7 @@ struct Gen {
 int generate(const Ode &ode, const tb_compile_opts_t &co, Layout &L, std::string &src, std::string &err) {
     const tb_ode_desc_t &d = ode.desc;
     if (co.order < 1 || co.order > 64) { err = "order must be in 1..64"; return TB_ERR_ARG; }
+    if (co.kind == TB_KIND_LYAPCOL) { err = "TB_KIND_LYAPCOL is built by the register-tiled generator only (tape too large, or TB_CF_ROLLED set)"; return TB_ERR_UNSUPPORTED; }
     if (co.kind == TB_KIND_LYAP && !d.has_jac) { err = "TB_KIND_LYAP needs a Jacobian description"; return TB_ERR_ARG; }
     if (co.kind == TB_KIND_EVENTS && TB_OPERAND_KIND(d.ev_g) == TB_K_NONE) { err = "TB_KIND_EVENTS needs an event function"; return TB_ERR_ARG; }
     Gen g(ode, co, L);

@@ -739,7 +739,9 @@ int generate_unrolled(const Ode &ode, const tb_compile_opts_t &co, Layout &L, st
     if (events) {
         const bool gate_ok = d.ev_gate_cmp == TB_GATE_ALWAYS || TB_OPERAND_KIND(d.ev_gate) == TB_K_X;
         if (d.ev_nops != 0 || TB_OPERAND_KIND(d.ev_g) != TB_K_X || !gate_ok) { err = "the unrolled generator covers events on state components"; return TB_ERR_UNSUPPORTED; }
-    } else if (co.kind != TB_KIND_PLAIN) { err = "the unrolled generator covers TB_KIND_PLAIN and TB_KIND_EVENTS"; return TB_ERR_UNSUPPORTED; }
+    } else if (co.kind == TB_KIND_LYAPCOL) {
+        if (d.dof < 2 || (d.dof & 1) || d.dof / 2 > 16) { err = "TB_KIND_LYAPCOL needs the column system [x; v] (an even number of components, at most 32)"; return TB_ERR_ARG; }
+    } else if (co.kind != TB_KIND_PLAIN) { err = "the unrolled generator covers TB_KIND_PLAIN, TB_KIND_EVENTS and TB_KIND_LYAPCOL"; return TB_ERR_UNSUPPORTED; }
     if (co.order < 1 || co.order > 40) { err = "order must be in 1..40 for the unrolled generator"; return TB_ERR_UNSUPPORTED; }
     if (d.dof > 16 || d.nops > 200) { err = "tape too large to unroll"; return TB_ERR_UNSUPPORTED; }
     std::set<int32_t> seen;
@@ -794,6 +796,7 @@ int generate_unrolled(const Ode &ode, const tb_compile_opts_t &co, Layout &L, st
     e.line("#define TB_MINB 1");
     e.line("#define TB_MODE %d", co.mode);
     e.line("#define TB_KIND %d", co.kind);
+    if (co.kind == TB_KIND_LYAPCOL) e.line("#define TB_NQ %d", d.dof / 2);
     e.line("#define TB_EV_NOPS 0");
     e.line("#define TB_JAC_NOPS 0");
     e.line("#define TB_BAR %d", (co.flags & 128) ? 1 : (co.flags & 1024) ? 2 : 0);

@@ -19,6 +19,11 @@
 #ifndef TB_BAR
 #define TB_BAR 0
 #endif
+/* TB_NQ: components of the ODE proper (step-size control, finiteness, outputs).  It equals TB_DOF except in the
+ * column-parallel Lyapunov kernel (TB_KIND == 3), whose jets cover [x; v] = 2*TB_NQ components.              */
+#ifndef TB_NQ
+#define TB_NQ TB_DOF
+#endif
 
 /* _stepsize: src/integrator/stepsize.jl:107-111   (eps/a)^(1/k).  Not inlined: the
  * double-double pow is ~300 instructions and is called 2*dof times per step.    */
@@ -136,7 +141,7 @@ __device__ __forceinline__ double tb_u_stepsize(const TbJets &J, const double *_
     if (a.reltol == 0.0) {
         double m1 = 0.0, m2 = 0.0;
 #pragma unroll
-        for (int c = 0; c < TB_DOF; c++) {
+        for (int c = 0; c < TB_NQ; c++) {
             m1 = fmax(m1, fabs(TB_X(c, TB_P - 1)));
             m2 = fmax(m2, fabs(TB_X(c, TB_P)));
         }
@@ -156,14 +161,14 @@ __device__ __forceinline__ double tb_u_stepsize(const TbJets &J, const double *_
          * NaN coefficients drop out of fmax here exactly as they drop out of min there.       */
 #pragma unroll
         for (int k = TB_P - 1; k <= TB_P; k++) {
-            double m = 0.0, ac[TB_DOF];
+            double m = 0.0, ac[TB_NQ];
 #pragma unroll
-            for (int c = 0; c < TB_DOF; c++) { ac[c] = fabs(TB_X(c, k)); m = fmax(m, ac[c]); }
+            for (int c = 0; c < TB_NQ; c++) { ac[c] = fabs(TB_X(c, k)); m = fmax(m, ac[c]); }
             if (m != 0.0) {
                 double hk = tb_stepsize_k(m, a.abstol, k);
                 const double thr = M_(m, 0.99999999999909051);
 #pragma unroll
-                for (int c = 0; c < TB_DOF; c++)
+                for (int c = 0; c < TB_NQ; c++)
                     if (ac[c] != m && ac[c] > thr) hk = fmin(hk, tb_stepsize_k(ac[c], a.abstol, k));
                 h = fmin(h, hk);
             }
@@ -172,7 +177,7 @@ __device__ __forceinline__ double tb_u_stepsize(const TbJets &J, const double *_
 #endif
     {
 #pragma unroll
-        for (int c = 0; c < TB_DOF; c++) {
+        for (int c = 0; c < TB_NQ; c++) {
             const double x0norm = fabs(TB_X(c, 0));
 #pragma unroll
             for (int k = TB_P - 1; k <= TB_P; k++) {
@@ -188,7 +193,7 @@ __device__ __forceinline__ double tb_u_stepsize(const TbJets &J, const double *_
         h = 0.0;
         double buf[TB_P + 1];
 #pragma unroll
-        for (int c = 0; c < TB_DOF; c++) {
+        for (int c = 0; c < TB_NQ; c++) {
 #pragma unroll
             for (int k = 0; k <= TB_P; k++) buf[k] = TB_X(c, k);
             h = fmax(h, tb_second_stepsize_arr(buf));
@@ -199,32 +204,32 @@ __device__ __forceinline__ double tb_u_stepsize(const TbJets &J, const double *_
 }
 #endif /* TB_VARIANT == 2 */
 
-#if TB_KIND == 2
+#if TB_KIND == 2 || TB_KIND == 3
 /* modifiedGS!(A, Q, R): src/lyapunovspectrum.jl:118-146, column-major n x n;
  * dot and norm as left-to-right sums (oracle: modifiedGS).                    */
 __device__ __forceinline__ void tb_mgs(const double *A, double *Q, double *Rd) {
-    double v[TB_DOF];
+    double v[TB_NQ];
 #pragma unroll
-    for (int j = 0; j < TB_DOF; j++) {
+    for (int j = 0; j < TB_NQ; j++) {
 #pragma unroll
-        for (int r = 0; r < TB_DOF; r++) v[r] = A[r + j * TB_DOF];
+        for (int r = 0; r < TB_NQ; r++) v[r] = A[r + j * TB_NQ];
 #pragma unroll
-        for (int i = 0; i < TB_DOF; i++) {
+        for (int i = 0; i < TB_NQ; i++) {
             if (i < j) {
-                double dot = M_(Q[0 + i * TB_DOF], v[0]);
+                double dot = M_(Q[0 + i * TB_NQ], v[0]);
 #pragma unroll
-                for (int r = 1; r < TB_DOF; r++) dot = A_(dot, M_(Q[r + i * TB_DOF], v[r]));
+                for (int r = 1; r < TB_NQ; r++) dot = A_(dot, M_(Q[r + i * TB_NQ], v[r]));
 #pragma unroll
-                for (int r = 0; r < TB_DOF; r++) v[r] = B_(v[r], M_(dot, Q[r + i * TB_DOF]));
+                for (int r = 0; r < TB_NQ; r++) v[r] = B_(v[r], M_(dot, Q[r + i * TB_NQ]));
             }
         }
         double ss = M_(v[0], v[0]);
 #pragma unroll
-        for (int r = 1; r < TB_DOF; r++) ss = A_(ss, M_(v[r], v[r]));
+        for (int r = 1; r < TB_NQ; r++) ss = A_(ss, M_(v[r], v[r]));
         double nrm = Q_(ss);
         Rd[j] = nrm;
 #pragma unroll
-        for (int r = 0; r < TB_DOF; r++) Q[r + j * TB_DOF] = D_(v[r], nrm);
+        for (int r = 0; r < TB_NQ; r++) Q[r + j * TB_NQ] = D_(v[r], nrm);
     }
 }
 #endif
@@ -279,6 +284,12 @@ struct TbTraj {
 #if TB_KIND == 2
     double lsum[TB_DOF], lam[TB_DOF], t00;
 #endif
+#if TB_KIND == 3
+    double lsum, lam, t00; /* this lane's exponent (column `lit` of the fundamental matrix) */
+    int lit;               /* lane in team = column index */
+    int leader;            /* warp lane of the team's first member */
+    unsigned tmask;        /* the team's lanes */
+#endif
     /* trange variant */
     long long iter;
     double t1;
@@ -287,7 +298,7 @@ struct TbTraj {
 __device__ __forceinline__ bool tb_isfinite_state(const double *x0) {
     bool fin = true;
 #pragma unroll
-    for (int c = 0; c < TB_DOF; c++) fin = fin && isfinite(x0[c]);
+    for (int c = 0; c < TB_NQ; c++) fin = fin && isfinite(x0[c]);
     return fin;
 }
 
@@ -299,6 +310,7 @@ __device__ __forceinline__ void tb_update_cache(double *__restrict__ smt, const 
 #endif /* variant 2: tb_u_jets reads x0 directly */
 }
 
+#if TB_KIND != 3
 /* returns true when the trajectory needs no step at all */
 __device__ __forceinline__ bool tb_traj_init(TbTraj &T, double *__restrict__ smt, const TbArgs &a, long long i) {
     T.i = i;
@@ -367,6 +379,8 @@ __device__ __forceinline__ bool tb_traj_init(TbTraj &T, double *__restrict__ smt
     return !(M_(T.sign, T.t0) < M_(T.sign, T.tmax));
 }
 
+#endif /* TB_KIND != 3 */
+
 /* variant-independent spelling of "the jets of the current step" */
 #if TB_VARIANT == 1
 #define TB_JETS_DECL
@@ -388,6 +402,7 @@ __device__ __forceinline__ bool tb_traj_init(TbTraj &T, double *__restrict__ smt
 #define TB_UNROLL_V2 _Pragma("unroll")
 #endif
 
+#if TB_KIND != 3
 __device__ __forceinline__ void tb_store_step(const TbTraj &T, const double *__restrict__ smt, const TbArgs &a) {
     /* called after nsteps += 1: column nsteps-1 */
     const long long s = T.nsteps - 1, N = a.N;
@@ -646,6 +661,143 @@ extern "C" __global__ void __launch_bounds__(TB_BT, TB_MINB) tb_ensemble_kernel(
     }
 }
 
+#else /* TB_KIND == 3 */
+/* ---- column-parallel Lyapunov spectrum (TB_KIND == 3) ---------------------------------------------
+ * lyap_taylorinteg!: src/lyapunovspectrum.jl:340-429; lyap_taylorstep! 226-274; lyap_jetcoeffs! 161-211.
+ * A TEAM of TB_NQ consecutive lanes integrates one trajectory.  Lane j carries the state x (all lanes
+ * compute identical x jets) and column j of the fundamental matrix; the generated jets are those of the
+ * column system [x; v], v' = J(x) v, whose sums follow the reference's accumulation order, so every
+ * coefficient has the bits of the single-thread kernel (TB_KIND == 2) and of the oracle.  Per step the
+ * columns are exchanged with warp shuffles and every lane runs the same modified Gram-Schmidt.       */
+#define TB_TEAM TB_NQ
+#define TB_TPW (32 / TB_TEAM) /* teams per warp */
+
+__device__ __forceinline__ bool tb_traj_init(TbTraj &T, double *__restrict__ smt, const TbArgs &a, long long i) {
+    T.i = i;
+    const long long N = a.N;
+#pragma unroll
+    for (int c = 0; c < TB_NQ; c++) T.x0[c] = a.q0[(long long)c * N + i];
+    /* init_cache_lyap: state = [q; vec(I)]  src/integrator/cache.jl:320-369; this lane holds column `lit` */
+#pragma unroll
+    for (int r = 0; r < TB_NQ; r++) T.x0[TB_NQ + r] = (r == T.lit) ? 1.0 : 0.0;
+    T.lsum = 0.0;
+    T.lam = 0.0;
+#pragma unroll
+    for (int j = 0; j < TB_NPAR; j++) T.par[j] = a.params_per_traj ? a.params[(long long)j * N + i] : a.params[j];
+    T.nsteps = 1;
+    T.st = 0;
+    T.iter = 2;
+    T.t0 = a.t0;
+    T.tmax = a.tmax;
+    T.t1 = 0.0;
+    T.sign = copysign(1.0, B_(T.tmax, T.t0));
+    T.t00 = T.t0;
+    if (T.lit == 0) {
+        if (a.tv) a.tv[i] = T.t0;
+        if (a.xv)
+#pragma unroll
+            for (int c = 0; c < TB_NQ; c++) a.xv[((long long)c * a.stride) * N + i] = T.x0[c];
+    }
+    if (a.lambda_v) a.lambda_v[((long long)T.lit * a.stride) * N + i] = 0.0;
+    return !(M_(T.sign, T.t0) < M_(T.sign, T.tmax));
+}
+
+/* value held by column `col` of a per-lane array indexed [r + col * TB_NQ], col known only at run time */
+__device__ __forceinline__ double tb_pick_col(const double *M, int r, int col) {
+    double v = M[r];
+#pragma unroll
+    for (int j = 1; j < TB_NQ; j++) v = (col == j) ? M[r + j * TB_NQ] : v;
+    return v;
+}
+
+__device__ __forceinline__ bool tb_traj_step(TbTraj &T, double *__restrict__ smt, const TbArgs &a, const bool live) {
+    TB_JETS_DECL
+    TB_COMPUTE_JETS(T);
+    double dt = TB_STEPSIZE(a); /* over the TB_NQ components of x only (lyapunovspectrum.jl:262) */
+    dt = M_(T.sign, fmin(dt, M_(T.sign, B_(T.tmax, T.t0))));
+    double xn[TB_NX];
+    TB_UNROLL_V2
+    for (int c = 0; c < TB_NX; c++) xn[c] = TB_HORNER(c, dt);
+    /* the evolved fundamental matrix, column j from lane leader + j */
+    double A[TB_NQ * TB_NQ], QH[TB_NQ * TB_NQ], Rd[TB_NQ];
+#pragma unroll
+    for (int j = 0; j < TB_NQ; j++)
+#pragma unroll
+        for (int r = 0; r < TB_NQ; r++) A[r + j * TB_NQ] = __shfl_sync(T.tmask, xn[TB_NQ + r], T.leader + j);
+    tb_mgs(A, QH, Rd);
+    T.t0 = A_(T.t0, dt);
+    const double tspan = B_(T.t0, T.t00);
+    T.nsteps += 1;
+    double rd = Rd[0];
+#pragma unroll
+    for (int j = 1; j < TB_NQ; j++) rd = (T.lit == j) ? Rd[j] : rd;
+    T.lsum = A_(T.lsum, tb_log(rd));
+    T.lam = D_(T.lsum, tspan);
+    {
+        const long long s = T.nsteps - 1, N = a.N;
+        const bool st_ok = s < a.stride;
+        if (T.lit == 0 && st_ok) {
+            if (a.tv) a.tv[s * N + T.i] = T.t0;
+            if (a.xv)
+#pragma unroll
+                for (int c = 0; c < TB_NQ; c++) a.xv[((long long)c * a.stride + s) * N + T.i] = xn[c];
+        }
+        if (a.lambda_v && st_ok) a.lambda_v[((long long)T.lit * a.stride + s) * N + T.i] = T.lam;
+    }
+#pragma unroll
+    for (int c = 0; c < TB_NQ; c++) T.x0[c] = xn[c];
+#pragma unroll
+    for (int r = 0; r < TB_NQ; r++) T.x0[TB_NQ + r] = tb_pick_col(QH, r, T.lit);
+    if (T.nsteps > a.maxsteps) { T.st |= TB_ST_MAXSTEPS; return true; }
+    if (!tb_isfinite_state(T.x0)) { T.st |= TB_ST_NONFINITE; return true; }
+    return !(M_(T.sign, T.t0) < M_(T.sign, T.tmax));
+}
+
+__device__ __forceinline__ void tb_traj_finish(const TbTraj &T, const TbArgs &a) {
+    const long long N = a.N, i = T.i;
+    if (T.lit == 0) {
+        if (a.xfinal)
+#pragma unroll
+            for (int c = 0; c < TB_NQ; c++) a.xfinal[(long long)c * N + i] = T.x0[c];
+        if (a.tfinal) a.tfinal[i] = T.t0;
+        if (a.nsteps) a.nsteps[i] = T.nsteps - 1;
+        if (a.status) a.status[i] = T.st;
+    }
+    if (a.lambda) a.lambda[(long long)T.lit * N + i] = T.lam;
+}
+
+/* Persistent teams: every team pulls trajectory indices from the global queue (leader lane does the
+ * atomic, the index is broadcast inside the team) and refills as soon as its trajectory ends; lanes
+ * beyond the last whole team of a warp (32 % TB_NQ of them) stay idle.  The loop ends on a warp vote. */
+extern "C" __global__ void __launch_bounds__(TB_BT, TB_MINB) tb_ensemble_kernel(const TbArgs a) {
+    extern __shared__ double tb_sm[];
+    double *__restrict__ smt = tb_sm + threadIdx.x;
+    const unsigned full = 0xffffffffu;
+    const int lane = threadIdx.x & 31;
+    const bool member = lane < TB_TPW * TB_TEAM;
+    TbTraj T;
+    T.lit = lane % TB_TEAM;
+    T.leader = lane - T.lit;
+    T.tmask = member ? ((TB_TEAM == 32 ? 0xffffffffu : ((1u << TB_TEAM) - 1u)) << T.leader) : (1u << lane);
+    bool have = false, more = member;
+    for (;;) {
+        while (!have && more) {
+            long long i = 0;
+            if (T.lit == 0) i = (long long)atomicAdd(a.counter, 1ull);
+            i = __shfl_sync(T.tmask, i, T.leader);
+            if (i >= a.N) { more = false; break; }
+            have = true;
+            if (tb_traj_init(T, smt, a, i)) { tb_traj_finish(T, a); have = false; }
+        }
+        if (!__any_sync(full, have)) break;
+        if (have) {
+            if (tb_traj_step(T, smt, a, true)) { tb_traj_finish(T, a); have = false; }
+        }
+    }
+}
+#endif /* TB_KIND == 3 */
+
+#if TB_KIND != 3
 /* tb_jet: one taylorstep! (src/integrator/taylorstep.jl:59-82) per trajectory;
  * jets x[dof x (P+1) x N] and the step size.                                   */
 extern "C" __global__ void __launch_bounds__(TB_BT, TB_MINB) tb_jet_kernel(const TbArgs a) {
@@ -673,5 +825,10 @@ extern "C" __global__ void __launch_bounds__(TB_BT, TB_MINB) tb_jet_kernel(const
         }
     }
 }
+
+#else
+/* the jet probe is not offered for the column system (tb_jet returns TB_ERR_UNSUPPORTED) */
+extern "C" __global__ void tb_jet_kernel(const TbArgs a) {}
+#endif
 
 #endif /* TB_DEVICE_DRV_CUH */

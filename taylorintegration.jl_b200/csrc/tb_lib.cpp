@@ -296,7 +296,9 @@ static void fill_args(TbArgs &a, int64_t N, const double *q0, const double *para
 static int launch(tb_kernel *k, Loaded *l, CUfunction f, TbArgs &a, bool persistent, cudaStream_t stream) {
     Driver &d = driver();
     const int bt = k->L.block_threads;
-    long long want = (a.N + bt - 1) / bt;
+    long long per_block = bt; /* trajectories one block holds at a time */
+    if (k->co.kind == TB_KIND_LYAPCOL) { const int nq = k->ode.desc.dof / 2; per_block = (long long)(bt / 32) * (32 / nq); }
+    long long want = (a.N + per_block - 1) / per_block;
     long long cap = (long long)l->sm_count * k->L.blocks_per_sm;
     unsigned grid = (unsigned)std::max<long long>(1, persistent ? std::min(want, cap) : std::min<long long>(want, cap * 4));
     void *params[1] = {&a};
@@ -350,7 +352,9 @@ static int integrate_host(tb_kernel *k, int64_t N, const double *q0, const doubl
     Loaded *l = nullptr;
     int rc = ensure_loaded(k, &l);
     if (rc) return rc;
-    const size_t dof = d.dof, n = (size_t)N, np1 = k->co.order + 1;
+    const bool lyapcol = k->co.kind == TB_KIND_LYAPCOL;
+    const size_t dof = lyapcol ? d.dof / 2 : d.dof, n = (size_t)N, np1 = k->co.order + 1;
+    if (lyapcol && out->psol) { set_error("TB_KIND_LYAPCOL has no dense output"); return TB_ERR_UNSUPPORTED; }
     const size_t stride = opts->steps_stride ? opts->steps_stride : opts->maxsteps + 1;
     const size_t cap = opts->event_capacity > 0 ? opts->event_capacity : (size_t)(opts->maxsteps + 1);
     const size_t npar_elems = d.npar ? (opts->params_per_traj ? (size_t)d.npar * n : (size_t)d.npar) : 0;
@@ -375,7 +379,7 @@ static int integrate_host(tb_kernel *k, int64_t N, const double *q0, const doubl
         want(out->gresids, (void **)&dv.gresids, cap * n * 8);
         want(out->nevents, (void **)&dv.nevents, n * 4);
     }
-    if (k->co.kind == TB_KIND_LYAP) {
+    if (k->co.kind == TB_KIND_LYAP || lyapcol) {
         want(out->lambda, (void **)&dv.lambda, dof * n * 8);
         if (!trange) want(out->lambda_v, (void **)&dv.lambda_v, dof * stride * n * 8);
     }
@@ -635,6 +639,7 @@ double tb_last_kernel_ms(void) { return g_last_ms; }
 int tb_jet(tb_kernel_t *k, int64_t N, const double *q0, const double *params, double t0, const tb_opts_t *opts,
            double *xjet, double *dt) {
     if (!k || !opts || !q0 || N < 0) { set_error("tb_jet: bad argument"); return TB_ERR_ARG; }
+    if (k->co.kind == TB_KIND_LYAPCOL) { set_error("tb_jet: not offered for TB_KIND_LYAPCOL kernels"); return TB_ERR_UNSUPPORTED; }
     if (N == 0) return TB_OK;
     Loaded *l = nullptr;
     int rc = ensure_loaded(k, &l);

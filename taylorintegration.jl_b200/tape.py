@@ -541,3 +541,68 @@ def taylorize(f: Callable, dof: int, npar: int = 0, *, event: Optional[Callable]
         tape.jac_ops = tr.segments[2]
     tape.ntmp = tr.ntmp
     return tape
+
+
+def lyap_column_tape(tape: Tape) -> Optional[Tape]:
+    """The column system of `lyap_jetcoeffs!` (src/lyapunovspectrum.jl:161-211) as a plain tape.
+
+    State `[x; v]` with `x' = f(x)` (the tape itself) and `v' = J(x) v` for ONE column `v` of the fundamental matrix:
+    `dv[i] = ((J[i,0]*v[0]) + J[i,1]*v[1]) + ...` in the reference's accumulation order (i3 ascending), every product a
+    full `mul!` with the Jacobian series first.  Constant / parameter entries multiply as numbers (the coefficients the
+    reference adds for their higher orders are exact zeros), structurally zero entries are skipped.  A team of `dof`
+    GPU lanes, one per column, integrates a trajectory with this tape (TB_KIND_LYAPCOL).
+
+    Returns None when an entry cannot be expressed with the same bits (a parameter scaled by c != +-1) or the system
+    is too large for the register-tiled generator; the caller then uses the single-thread TB_KIND_LYAP kernel.
+    """
+    if tape.jac is None:
+        return None
+    n = tape.dof
+    if n > 8 or n < 1:
+        return None
+    ops = [Op(o.op, o.res, o.a, o.b, o.aux, o.imm) for o in list(tape.ops) + list(tape.jac_ops)]
+    ntmp = tape.ntmp
+
+    def tmp() -> int:
+        nonlocal ntmp
+        ntmp += 1
+        return L.operand(L.K_TMP, ntmp - 1)
+
+    imm_operand = L.operand(L.K_IMM, 0)
+    for i in range(n):
+        acc = None  # operand holding the running sum
+        for m in range(n):
+            kind, operand, c = tape.jac[i * n + m]
+            v = L.operand(L.K_X, n + m)
+            neg = False
+            if kind == L.JAC_ZERO:
+                continue
+            if kind == L.JAC_CONST:
+                term = Op(L.OP_MUL, tmp(), imm_operand, v, 0, float(c))
+            elif kind == L.JAC_PAR:
+                if c not in (1.0, -1.0):
+                    return None
+                neg = c == -1.0  # (-p)*v and -(p*v) have the same bits
+                term = Op(L.OP_MUL, tmp(), operand, v)
+            elif kind == L.JAC_SERIES:
+                term = Op(L.OP_MUL, tmp(), operand, v)
+            else:
+                return None
+            ops.append(term)
+            t = term.res
+            if acc is None:
+                if neg:
+                    o = Op(L.OP_NEG, tmp(), t)
+                    ops.append(o)
+                    t = o.res
+                acc = t
+            else:
+                o = Op(L.OP_SUB if neg else L.OP_ADD, tmp(), acc, t)
+                ops.append(o)
+                acc = o.res
+        dxi = L.operand(L.K_DX, n + i)
+        if acc is None:
+            ops.append(Op(L.OP_ZERO, dxi, L.operand(L.K_X, n + i)))
+        else:
+            ops.append(Op(L.OP_IDENTITY, dxi, acc))
+    return Tape(2 * n, tape.npar, ntmp, ops, name=tape.name + "+column")

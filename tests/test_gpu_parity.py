@@ -150,6 +150,23 @@ def test_lorenz_lyapunov():
     assert np.array_equal(g.nsteps, o.nsteps)
     assert np.array_equal(g.xfinal, o.xfinal)
     assert np.array_equal(g.lam, o.lam)  # bar: 1e-6
+    # the call above ran the column-parallel kernel (teams of 3 lanes, TB_KIND_LYAPCOL); the single-thread kernel
+    # (TB_KIND_LYAP) must give the same bits, and per-step output must agree between the two as well
+    g1 = tb.lyap_taylorinteg(tape, q0, 0.0, 5.0, 28, 1e-20, pars, maxsteps=2000, kernel_opts={"columns": False})
+    assert np.array_equal(g1.nsteps, o.nsteps) and np.array_equal(g1.xfinal, o.xfinal) and np.array_equal(g1.lam, o.lam)
+    s1 = tb.lyap_taylorinteg(tape, np.array([19.0, 20.0, 50.0]), 0.0, 20.0, 28, 1e-20, par, maxsteps=2000,
+                             kernel_opts={"columns": False})
+    assert np.array_equal(s.t, s1.t) and np.array_equal(s.x, s1.x) and np.array_equal(s.lam, s1.lam)
+    # fast mode through the column kernel: exponents within the reference's own tolerance
+    f = tb.lyap_taylorinteg(tape, np.array([19.0, 20.0, 50.0]), 0.0, 20.0, 28, 1e-20, par, maxsteps=2000, mode="fast")
+    assert np.max(np.abs(f.lam[-1] - lam)) < 1e-4
+
+
+def test_lyapunov_column_tape_structure():
+    from taylorintegration_b200.tape import lyap_column_tape
+    col = lyap_column_tape(P.lorenz_tape())
+    assert col is not None and col.dof == 6 and col.npar == 3 and col.jac is None
+    assert lyap_column_tape(P.kepler_tape()) is None  # no Jacobian requested
 
 
 def test_every_primitive_matches_oracle():
