@@ -294,6 +294,16 @@ def run_b200(a):
     if rank != 0:
         return
     ms_kernel = float(np.mean(kms))
+    # DRAM traffic of one launch of this kernel on this workload, from the committed `ncu --set full` capture
+    # (profiles/ncu_traffic.json: dram__bytes_read.sum + dram__bytes_write.sum); null when no capture matches
+    traffic = None
+    try:
+        with open(os.path.join(ROOT, "profiles", "ncu_traffic.json")) as f:
+            t = json.load(f)
+        if (t.get("ntraj"), t.get("periods"), t.get("order"), t.get("mode")) == (a.ntraj, a.periods, a.order, a.mode):
+            traffic = t["dram_bytes_per_launch"]
+    except (OSError, ValueError, KeyError):
+        pass
     ach_tf = (total_steps / world) * KEPLER_FLOPS_PER_STEP / (ms_kernel * 1e-3) / 1e12
     info = k.info()
     line = {"metric": "kepler_order28_ensemble_trajectory_steps_per_s", "value": value, "unit": "trajectory-steps/s",
@@ -302,7 +312,8 @@ def run_b200(a):
             "config": config_dict(a, {"trajectory_steps_per_pass": total_steps, "all_ok": ok, "kernel": info}),
             "clocks": clk, "e2e": e2e, "gpu_launches": int(launches),
             "roofline": {"bound": "fp64", "achieved": ach_tf, "peak": peak_tf, "unit": "TFLOP/s",
-                         "frac": ach_tf / peak_tf, "traffic": None,
+                         "frac": ach_tf / peak_tf, "traffic": traffic,
+                         "algorithmic_bytes_per_launch": int(N * (4 * 8 + 4 * 8 + 8 + 8 + 4) + 8),
                          "peak_source": "tb_fp64_peak: register-only DFMA chains measured in this run "
                                         "(MEASURED_PEAKS.json has no FP64 entry; nominal 37.2 TFLOP/s)",
                          "kernel": "tb_ensemble_kernel", "kernel_ms": ms_kernel,
