@@ -76,6 +76,7 @@ struct SeriesInfo {
     int base = 0;     /* shared memory: coefficient k lives at double (base + k) of the thread's column */
     int trim = 0;     /* shared memory: coefficients 0..trim-1 are not stored (exactly recoverable, see analyse) */
     int32_t dx = 0;   /* trimmed state jet: its derivative series */
+    int kreg = 0;     /* PL_REG: coefficients 0..kreg-1 live in registers, kreg..len-1 in shared memory (split series) */
 };
 
 struct UGen {
@@ -97,6 +98,7 @@ struct UGen {
         ser[o].reads += w;
     }
     bool derive_x = true;
+    bool split = false;   /* registers hold the LOW coefficients of every recurrence-read series (see analyse) */
     bool trim_x = false;  /* parity: do not store x[0], x[1], x[2] of state jets that only Horner / stepsize read */
     int smem_doubles = 0; /* shared-memory doubles per trajectory */
     void analyse(int reg_budget) {
@@ -138,8 +140,25 @@ struct UGen {
         for (auto &pr : order) {
             SeriesInfo &si = ser[pr.second];
             si.len = P + 1;
-            if (si.reads > 0 && used + si.len <= reg_budget) { si.place = PL_REG; si.id = nreg++; used += si.len; }
+            if (si.reads > 0 && used + si.len <= reg_budget) { si.place = PL_REG; si.id = nreg++; used += si.len; si.kreg = si.len; }
             else { si.place = PL_SMEM; si.id = nsm++; }
+        }
+        if (split) {
+            /* Split placement.  Coefficient j of a series read by recurrences is read P - j times per step, so the
+             * top coefficients are cold: the register budget is spread over the LOW coefficients of ALL such series
+             * and only their high coefficients go to shared memory.  Same registers, ~3x fewer LDS than keeping some
+             * series whole in registers and the others whole in shared memory.                                      */
+            int nread = 0;
+            for (auto &pr : order) if (ser[pr.second].reads > 0) nread++;
+            if (nread > 0) {
+                int K = std::min(P + 1, std::max(1, reg_budget / nread));
+                nreg = 0; nsm = 0;
+                for (auto &pr : order) {
+                    SeriesInfo &si = ser[pr.second];
+                    if (si.reads > 0) { si.place = PL_REG; si.id = nreg++; si.kreg = std::min(K, si.len); }
+                    else { si.place = PL_SMEM; si.id = nsm++; si.kreg = 0; }
+                }
+            }
         }
         /* trimmed state jets: x[0] is the state itself, x[1] = dx[0]/1 and x[2] = dx[1]/2 are exact scalings of
          * stored dx coefficients, so a state jet that no recurrence reads keeps only x[3..P] in shared memory.
@@ -162,10 +181,22 @@ struct UGen {
                 si.base = run - si.trim;
                 run += si.len - si.trim;
             }
+        for (auto &kv : ser) { /* high coefficients of split register series */
+            SeriesInfo &si = kv.second;
+            if (si.place != PL_REG || si.kreg >= si.len) continue;
+            si.base = run - si.kreg;
+            run += si.len - si.kreg;
+        }
         smem_doubles = run;
     }
     std::string sref(const SeriesInfo &si, const std::string &k) const { return fmt("SB(%d, %s)", si.base, k.c_str()); }
     std::string sref(const SeriesInfo &si, int k) const { return fmt("SB(%d, %d)", si.base, k); }
+    /* coefficient `k` (an expression that folds to a constant once the caller is unrolled) of a stored series */
+    std::string dynref(const SeriesInfo &si, const std::string &k) const {
+        if (si.place != PL_REG) return sref(si, k);
+        if (si.kreg >= si.len) return fmt("J.r%d[%s]", si.id, k.c_str());
+        return fmt("(%s < %d ? J.r%d[%s < %d ? %s : 0] : %s)", k.c_str(), si.kreg, si.id, k.c_str(), si.kreg, k.c_str(), sref(si, k).c_str());
+    }
 
     /* ---- values ---------------------------------------------------------------
      * A coefficient (series o, index idx) is referred to by the NAME of the local
@@ -197,7 +228,7 @@ struct UGen {
             err = "internal: series operand not stored";
             return "0.0";
         }
-        if (it->second.place == PL_REG) return fmt("J.r%d[%d]", it->second.id, r.idx);
+        if (it->second.place == PL_REG && r.idx < it->second.kreg) return fmt("J.r%d[%d]", it->second.id, r.idx);
         auto lt = loaded.find(Key(r.o, r.idx));
         if (lt != loaded.end()) return lt->second;
         std::string n = fmt("l%d", tmpc++);
@@ -583,7 +614,8 @@ struct UGen {
     void store(Em &e, int32_t o, int k, const std::string &v) {
         auto it = ser.find(o);
         if (it == ser.end()) return;
-        if (it->second.place == PL_REG) e.line("  J.r%d[%d] = %s;", it->second.id, k, v.c_str());
+        if (it->second.place == PL_REG && k < it->second.kreg) e.line("  J.r%d[%d] = %s;", it->second.id, k, v.c_str());
+        else if (it->second.place == PL_REG) e.line("  %s = %s;", sref(it->second, k).c_str(), v.c_str());
         else if (it->second.place == PL_SMEM && k >= it->second.trim) e.line("  %s = %s;", sref(it->second, k).c_str(), v.c_str());
     }
 
@@ -707,17 +739,16 @@ struct UGen {
         e.line("  switch (c) {");
         for (int c = 0; c < d.dof; c++) {
             const SeriesInfo &si = ser[TB_OPERAND(TB_K_X, c)];
-            if (si.place == PL_REG) e.line("    case %d: return J.r%d[k];", c, si.id);
+            if (si.place == PL_REG) e.line("    case %d: return %s;", c, dynref(si, "k").c_str());
             else if (si.place == PL_SMEM && si.trim == 0) e.line("    case %d: return %s;", c, sref(si, "k").c_str());
             else if (si.place == PL_SMEM) {
                 const SeriesInfo &di = ser[si.dx];
-                std::string r0 = di.place == PL_REG ? fmt("J.r%d[0]", di.id) : sref(di, 0);
-                std::string r1 = di.place == PL_REG ? fmt("J.r%d[1]", di.id) : sref(di, 1);
+                std::string r0 = dynref(di, "0"), r1 = dynref(di, "1");
                 e.line("    case %d: return k == 0 ? x0[%d] : (k == 1 ? M_(%s, 1.0) : (k == 2 ? M_(%s, 0.5) : %s));", c, c, r0.c_str(),
                        r1.c_str(), sref(si, "k").c_str());
             } else {
                 const SeriesInfo &di = ser[TB_OPERAND(TB_K_DX, c)];
-                std::string ref = di.place == PL_REG ? fmt("J.r%d[k - 1]", di.id) : sref(di, "k - 1");
+                std::string ref = dynref(di, "(k - 1)");
                 if (fast) e.line("    case %d: return k == 0 ? x0[%d] : %s * (1.0 / (double)k);", c, c, ref.c_str());
                 else e.line("    case %d: return k == 0 ? x0[%d] : tb_divc(%s, k);", c, c, ref.c_str());
             }
@@ -762,6 +793,7 @@ int generate_unrolled(const Ode &ode, const tb_compile_opts_t &co, Layout &L, st
     if (co.reg_budget < 0) budget = 0;
     g.derive_x = parity ? (co.flags & 512) != 0 : !(co.flags & 256);
     g.trim_x = parity && co.kind == TB_KIND_PLAIN && !(co.flags & 4096);
+    g.split = (co.flags & 8192) != 0;
     g.analyse(budget);
     L.variant = 2;
     L.nx = d.dof;
@@ -804,7 +836,11 @@ int generate_unrolled(const Ode &ode, const tb_compile_opts_t &co, Layout &L, st
     e.s += embedded_device_pre();
     e.line("/* placement: %d series in registers, %d in shared memory */", g.nreg, g.nsm);
     e.line("struct TbJets {");
-    for (int i = 0; i < g.nreg; i++) e.line("  double r%d[%d];", i, np1);
+    for (int i = 0; i < g.nreg; i++) {
+        int kr = np1;
+        for (auto &kv : g.ser) if (kv.second.place == PL_REG && kv.second.id == i) kr = kv.second.kreg;
+        e.line("  double r%d[%d];", i, kr);
+    }
     if (g.nreg == 0) e.line("  int unused;");
     e.line("};");
     g.emit_jets(e);
