@@ -569,6 +569,7 @@ def lyap_column_tape(tape: Tape) -> Optional[Tape]:
         return L.operand(L.K_TMP, ntmp - 1)
 
     imm_operand = L.operand(L.K_IMM, 0)
+    negated = {o.res: o.a for o in ops if o.op == L.OP_NEG and L.operand_kind(o.a) in (L.K_X, L.K_DX, L.K_TMP)}
     for i in range(n):
         acc = None  # operand holding the running sum
         for m in range(n):
@@ -585,6 +586,10 @@ def lyap_column_tape(tape: Tape) -> Optional[Tape]:
                 neg = c == -1.0  # (-p)*v and -(p*v) have the same bits
                 term = Op(L.OP_MUL, tmp(), operand, v)
             elif kind == L.JAC_SERIES:
+                if operand in negated:
+                    # J = -s: mul!(-s, v) and -mul!(s, v) have the same bits (every product and partial sum changes
+                    # sign only), and s is usually a series the trajectory part already keeps: one stored series less
+                    operand, neg = negated[operand], True
                 term = Op(L.OP_MUL, tmp(), operand, v)
             else:
                 return None
@@ -605,4 +610,13 @@ def lyap_column_tape(tape: Tape) -> Optional[Tape]:
             ops.append(Op(L.OP_ZERO, dxi, L.operand(L.K_X, n + i)))
         else:
             ops.append(Op(L.OP_IDENTITY, dxi, acc))
+    # drop entries nothing reads any more (e.g. the negated Jacobian series replaced above)
+    while True:
+        used = set()
+        for o in ops:
+            used.update((o.a, o.b))
+        keep = [o for o in ops if L.operand_kind(o.res) == L.K_DX or o.res in used or (o.aux and o.aux in used)]
+        if len(keep) == len(ops):
+            break
+        ops = keep
     return Tape(2 * n, tape.npar, ntmp, ops, name=tape.name + "+column")
