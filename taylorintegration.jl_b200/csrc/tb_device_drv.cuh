@@ -244,6 +244,19 @@ __device__ __forceinline__ double tb_gder(const double *__restrict__ smt, int eo
 }
 /* evaluate!(g_dg, dt): G = derivative(g, eo), dG = derivative(G), both Horner */
 __device__ __forceinline__ void tb_eval_g_dg(const double *__restrict__ smt, int eo, double dt, double *gv, double *dgv) {
+    if (eo == 0) {
+        /* the usual case (eventorder = 0, G = g): same operations with static indices, each coefficient read once */
+        double gk1 = TB_EV_G(TB_P), s0 = gk1, ds0 = 0.0;
+#pragma unroll
+        for (int k = TB_P - 1; k >= 0; k--) {
+            ds0 = A_(M_(ds0, dt), M_((double)(k + 1), gk1));
+            gk1 = TB_EV_G(k);
+            s0 = A_(M_(s0, dt), gk1);
+        }
+        *gv = s0;
+        *dgv = ds0;
+        return;
+    }
     double s = tb_gder(smt, eo, TB_P), ds = 0.0; /* dG[P] = 0 */
     for (int k = TB_P - 1; k >= 0; k--) {
         double Gk1 = tb_gder(smt, eo, k + 1);
