@@ -14,6 +14,7 @@
 
 #include <algorithm>
 #include <cstdint>
+#include <cstdlib>
 #include <map>
 #include <string>
 #include <vector>
@@ -235,7 +236,7 @@ __device__ __forceinline__ double wide_horner(const double *X, int P, double dt)
     return s;
 }
 
-template <bool FAST> __global__ void __launch_bounds__(256) wide_kernel(const WArgs a) {
+template <bool FAST, int MINB> __global__ void __launch_bounds__(256, MINB) wide_kernel(const WArgs a) {
     __shared__ double red[8];
     __shared__ unsigned long long s_idx;
     const int tid = threadIdx.x, nth = blockDim.x, P = a.P, np1 = P + 1;
@@ -563,9 +564,18 @@ int tb_wide_integrate(tb_wide_t *w, int64_t N, const double *q0, const double *p
     const bool fast = w->mode == TB_MODE_FAST;
     int threads = ((std::max(w->maxwidth, 32) + 31) / 32) * 32;
     if (threads > 256) threads = 256;
+    /* the kernel waits on L1/L2 loads of its global-memory workspace (ncu: long_scoreboard 21 per issue at 2 CTAs
+     * per SM), so the register budget is capped to fit 8 CTAs (64 warps) per SM: many-spin 1.6e5 -> 3.2e5 (4 CTAs)
+     * -> 4.3e5 (8 CTAs) trajectory-steps/s at 2048 members.  TB_WIDE_MINB=2|4 select the wider register budgets. */
+    int minb = 8;
+    if (const char *e = getenv("TB_WIDE_MINB")) { const int v = atoi(e); minb = v == 2 ? 2 : (v == 4 ? 4 : 8); }
     int bps = 1;
-    if (fast) TB_CUDA(cudaOccupancyMaxActiveBlocksPerMultiprocessor(&bps, wide_kernel<true>, threads, 0));
-    else TB_CUDA(cudaOccupancyMaxActiveBlocksPerMultiprocessor(&bps, wide_kernel<false>, threads, 0));
+    if (fast && minb == 8) TB_CUDA(cudaOccupancyMaxActiveBlocksPerMultiprocessor(&bps, wide_kernel<true, 8>, threads, 0));
+    else if (minb == 8) TB_CUDA(cudaOccupancyMaxActiveBlocksPerMultiprocessor(&bps, wide_kernel<false, 8>, threads, 0));
+    else if (fast && minb == 4) TB_CUDA(cudaOccupancyMaxActiveBlocksPerMultiprocessor(&bps, wide_kernel<true, 4>, threads, 0));
+    else if (fast) TB_CUDA(cudaOccupancyMaxActiveBlocksPerMultiprocessor(&bps, wide_kernel<true, 2>, threads, 0));
+    else if (minb == 4) TB_CUDA(cudaOccupancyMaxActiveBlocksPerMultiprocessor(&bps, wide_kernel<false, 4>, threads, 0));
+    else TB_CUDA(cudaOccupancyMaxActiveBlocksPerMultiprocessor(&bps, wide_kernel<false, 2>, threads, 0));
     bps = std::max(1, std::min(bps, 8));
     long long blocks = std::min<long long>((long long)nsm * bps, N);
     WArgs a{};
@@ -606,8 +616,12 @@ int tb_wide_integrate(tb_wide_t *w, int64_t N, const double *q0, const double *p
         cudaEventCreate(&e0);
         cudaEventCreate(&e1);
         cudaEventRecord(e0, 0);
-        if (fast) wide_kernel<true><<<(unsigned)blocks, threads>>>(a);
-        else wide_kernel<false><<<(unsigned)blocks, threads>>>(a);
+        if (fast && minb == 8) wide_kernel<true, 8><<<(unsigned)blocks, threads>>>(a);
+        else if (minb == 8) wide_kernel<false, 8><<<(unsigned)blocks, threads>>>(a);
+        else if (fast && minb == 4) wide_kernel<true, 4><<<(unsigned)blocks, threads>>>(a);
+        else if (fast) wide_kernel<true, 2><<<(unsigned)blocks, threads>>>(a);
+        else if (minb == 4) wide_kernel<false, 4><<<(unsigned)blocks, threads>>>(a);
+        else wide_kernel<false, 2><<<(unsigned)blocks, threads>>>(a);
         cudaEventRecord(e1, 0);
         tb::count_launch(1);
         fail(cudaGetLastError(), "wide_kernel launch");
