@@ -459,9 +459,19 @@ int eval_event(Work &w, std::vector<double> &gser, bool *flag) {
  * nrconvergencecriterion 147-152.                                             */
 int integ_events(Work &w, const double *q0, double t0, double tmax, const tb_opts_t &o, const StepOut *so,
                  double *xfinal, double *tfinal, int64_t *nsteps_out, int32_t *status,
-                 double *tevents, double *xevents /*[dof x cap]*/, double *gresids, int32_t *nevents_out, int cap) {
+                 double *tevents, double *xevents /*[dof x cap]*/, double *gresids, int32_t *nevents_out, int cap,
+                 const double *trange = nullptr, int64_t nt = 0, double *xvtr = nullptr /*[dof x nt]*/) {
     const int dof = w.d->dof, P = w.P, eo = o.eventorder;
-    std::vector<double> x0(q0, q0 + dof);
+    /* trange variant: src/rootfinding.jl:485-584 (in-step outputs 541-546, early exit on the last step 547-550) */
+    double t1 = 0.0;
+    int64_t iter = 2;
+    if (trange) {
+        t0 = trange[0]; t1 = trange[1]; tmax = trange[nt - 1];
+        const double nan = std::numeric_limits<double>::quiet_NaN();
+        for (int64_t j = 0; j < (int64_t)dof * nt; j++) xvtr[j] = nan;
+        for (int i = 0; i < dof; i++) xvtr[(size_t)i * nt] = q0[i];
+    }
+    std::vector<double> x0(q0, q0 + dof), x1(dof);
     update_cache(w, t0, x0.data(), dof);
     if (so && so->tv) so->tv[0] = t0;
     if (so && so->xv) for (int i = 0; i < dof; i++) so->xv[(size_t)i * so->stride] = q0[i];
@@ -485,6 +495,20 @@ int integ_events(Work &w, const double *q0, double t0, double tmax, const tb_opt
         if (rc) return rc;
         dt = sign_tstep * std::min(dt, sign_tstep * (tmax - t0));
         for (int i = 0; i < dof; i++) x0[i] = horner(w.X(i), P, dt);
+        if (trange) {
+            const double tnext = t0 + dt;
+            while (sign_tstep * t1 < sign_tstep * tnext) {
+                for (int i = 0; i < dof; i++) x1[i] = horner(w.X(i), P, t1 - t0);
+                for (int i = 0; i < dof; i++) xvtr[(size_t)i * nt + (iter - 1)] = x1[i];
+                iter += 1;
+                t1 = trange[iter - 1];
+            }
+            if (dt == tmax - t0) {
+                for (int i = 0; i < dof; i++) xvtr[(size_t)i * nt + (iter - 1)] = x0[i];
+                t0 = tnext;
+                break;
+            }
+        }
         if (so && so->psol)
             for (int i = 0; i < dof; i++)
                 for (int k = 0; k <= P; k++)
@@ -762,7 +786,10 @@ int tbo_integrate(const tb_ode_desc_t *d, int order, int kind, int math_mode, in
             int64_t ns = 0;
             int32_t st = 0, nev = 0;
             int rc = 0;
-            if (trange) rc = integ_trange(w, q.data(), trange, nt, o, xtr.data(), xf.data(), &tf, &ns, &st);
+            if (trange && kind == TB_KIND_EVENTS)
+                rc = integ_events(w, q.data(), t0, tmax, o, nullptr, xf.data(), &tf, &ns, &st, tev.data(), xev.data(),
+                                  gre.data(), &nev, cap, trange, nt, xtr.data());
+            else if (trange) rc = integ_trange(w, q.data(), trange, nt, o, xtr.data(), xf.data(), &tf, &ns, &st);
             else if (kind == TB_KIND_EVENTS)
                 rc = integ_events(w, q.data(), t0, tmax, o, want_steps ? &so : nullptr, xf.data(), &tf, &ns, &st,
                                   tev.data(), xev.data(), gre.data(), &nev, cap);

@@ -264,7 +264,12 @@ class EnsembleSolution:
     def trajectory(self, i: int) -> TaylorSolution:
         ns = int(self.nsteps[i])
         if self.x_trange is not None:
-            return TaylorSolution(t=None, x=self.x_trange[:, :, i].T.copy(), status=int(self.status[i]))
+            s = TaylorSolution(t=None, x=self.x_trange[:, :, i].T.copy(), status=int(self.status[i]))
+            if self.nevents is not None:
+                ne = int(self.nevents[i])
+                s.tevents, s.gresids = self.tevents[:ne, i].copy(), self.gresids[:ne, i].copy()
+                s.xevents = self.xevents[:, :ne, i].T.copy()
+            return s
         if self.t is None:
             raise ValueError("per-step output was not requested (output='final')")
         s = TaylorSolution(t=self.t[: ns + 1, i].copy(), x=self.x[:, : ns + 1, i].T.copy(), status=int(self.status[i]))
@@ -342,6 +347,12 @@ def _integrate(tape: Tape, kind: int, q0, t0, tmax, trange, order, abstol, param
         assert tr.size >= 2 and (np.all(d > 0) or np.all(d < 0)), "trange must be sorted"  # taylorinteg.jl:489,573
         sol.x_trange = np.empty((dof, tr.size, N))
         out.xv_trange = sol.x_trange.ctypes.data_as(L._DP)
+        if kind == L.KIND_EVENTS:  # taylorinteg(f!, g, q0, trange, ...): src/rootfinding.jl:440-584
+            sol.tevents, sol.gresids = np.zeros((cap, N)), np.zeros((cap, N))
+            sol.xevents, sol.nevents = np.zeros((dof, cap, N)), np.zeros(N, dtype=np.int32)
+            out.tevents, out.gresids = sol.tevents.ctypes.data_as(L._DP), sol.gresids.ctypes.data_as(L._DP)
+            out.xevents = sol.xevents.ctypes.data_as(L._DP)
+            out.nevents = sol.nevents.ctypes.data_as(C.POINTER(C.c_int32))
         if wide:
             L.check(lib.tb_wide_integrate(k.handle, N, _ptr(q), _ptr(par), float(tr[0]), float(tr[-1]), _ptr(tr), tr.size,
                                           C.byref(o), C.byref(out)), "tb_wide_integrate")
@@ -397,22 +408,21 @@ def taylorinteg(f, *args, maxsteps: int = 500, parse_eqs: bool = True, dense: bo
     dof = np.asarray(q0).shape[0]
     tape = _as_tape(f, dof, params, g=g)
     kind = L.KIND_EVENTS if g is not None else L.KIND_PLAIN
-    if trange is not None and kind != L.KIND_PLAIN:
-        raise NotImplementedError("the trange variant with events is not available yet")
     return _integrate(tape, kind, q0, t0, tmax, trange, int(order), abstol, params, maxsteps=maxsteps, dense=dense,
                       reltol=reltol, minstepsize=minstepsize, maxstepsize=maxstepsize, eventorder=eventorder,
                       newtoniter=newtoniter, nrabstol=nrabstol, event_capacity=event_capacity, mode=mode, output=output,
                       kernel_opts=kernel_opts)
 
 
-def taylorinteg_events(tape: Tape, q0, t0, tmax, order, abstol, params=None, **kw):
-    """Event-detecting driver for a pre-built `Tape` that already carries its event function."""
+def taylorinteg_events(tape: Tape, q0, t0, tmax, order, abstol, params=None, trange=None, **kw):
+    """Event-detecting driver for a pre-built `Tape` that already carries its event function; with `trange`
+    (t0, tmax ignored) it is the variant of src/rootfinding.jl:440-584."""
     kw.setdefault("maxsteps", 500)
     kw.setdefault("dense", True)
     kw.setdefault("reltol", 0.0)
     kw.setdefault("minstepsize", 0.0)
     kw.setdefault("maxstepsize", np.inf)
-    return _integrate(tape, L.KIND_EVENTS, q0, t0, tmax, None, int(order), abstol, params, **kw)
+    return _integrate(tape, L.KIND_EVENTS, q0, t0, tmax, trange, int(order), abstol, params, **kw)
 
 
 def lyap_taylorinteg(f, q0, t0, tmax, order, abstol, params=None, jacobianfunc=None, *, maxsteps: int = 500,

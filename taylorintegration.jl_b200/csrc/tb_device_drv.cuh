@@ -501,7 +501,31 @@ __device__ __forceinline__ bool tb_traj_step(TbTraj &T, double *__restrict__ smt
     double xn[TB_DOF];
 #pragma unroll
     for (int c = 0; c < TB_DOF; c++) xn[c] = TB_HORNER(c, dt);
-    tb_store_psol(T, TB_JETS_ARGS, a);
+    if (a.trange) {
+        /* the trange variant with events, src/rootfinding.jl:530-549: in-step outputs first; the step that lands
+         * on tmax stores its end point and leaves the loop BEFORE the event test of that step                  */
+        const double tnext = A_(T.t0, dt);
+        const long long N = a.N;
+        while (M_(T.sign, T.t1) < M_(T.sign, tnext)) {
+            const double d1 = B_(T.t1, T.t0);
+            if (a.xv_trange) {
+                TB_UNROLL_V2
+                for (int c = 0; c < TB_DOF; c++)
+                    a.xv_trange[((long long)c * a.nt + (T.iter - 1)) * N + T.i] = TB_HORNER(c, d1);
+            }
+            T.iter += 1;
+            T.t1 = a.trange[T.iter - 1];
+        }
+        if (dt == B_(T.tmax, T.t0)) {
+            if (a.xv_trange)
+                for (int c = 0; c < TB_DOF; c++) a.xv_trange[((long long)c * a.nt + (T.iter - 1)) * N + T.i] = xn[c];
+#pragma unroll
+            for (int c = 0; c < TB_DOF; c++) T.x0[c] = xn[c];
+            T.t0 = tnext;
+            return true;
+        }
+    } else
+        tb_store_psol(T, TB_JETS_ARGS, a);
 #if TB_VARIANT == 1
     const bool f_now = tb_eval_event(smt, T.par, T.t0);
     const double g_now = TB_EV_G(eo);

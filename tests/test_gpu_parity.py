@@ -131,6 +131,24 @@ def test_pendulum_events():
         assert np.array_equal(g.gresids[:n, i], o.gresids[:n, i])
 
 
+def test_events_with_trange_variant():
+    # taylorinteg(f!, g, q0, trange, ...): src/rootfinding.jl:440-584
+    tape = P.pendulum_tape()
+    tr = np.linspace(0.0, 3 * T_PEND, 25)
+    q0 = np.stack([np.linspace(0.4, 2.9, 70), np.zeros(70)])
+    g = tb.taylorinteg_events(tape, q0, None, None, 28, 1e-20, trange=tr, maxsteps=1000, event_capacity=16)
+    o = oracle.integrate(tape, 28, q0, kind=L.KIND_EVENTS, trange=tr, abstol=1e-20, maxsteps=1000, event_capacity=16)
+    assert np.array_equal(g.nevents, o.nevents) and g.nevents.max() > 3
+    for i in range(70):
+        ne = g.nevents[i]
+        assert np.array_equal(g.tevents[:ne, i], o.tevents[:ne, i]) and np.array_equal(g.xevents[:, :ne, i], o.xevents[:, :ne, i])
+        assert np.array_equal(g.gresids[:ne, i], o.gresids[:ne, i])
+    assert np.array_equal(g.x_trange, o.x_trange) and np.array_equal(g.nsteps, o.nsteps) and np.array_equal(g.xfinal, o.xfinal)
+    one = tb.taylorinteg(P.pendulum, lambda dx, x, p, t: (True, x[1]), np.array([1.3, 0.0]), tr, 28, 1e-20, maxsteps=1000)
+    assert one.x.shape == (25, 2) and len(one.tevents) == 5
+    assert np.max(np.abs(one.tevents - np.arange(1, 6) * T_PEND / 2)) < 1e-13
+
+
 def test_python_function_front_end_with_event_and_gate():
     # the reference's call shape taylorinteg(f, g, q0, t0, tmax, order, abstol) (rootfinding.jl:301-345)
     g_gate = lambda dx, x, p, t: (x[0] > 0, x[1])  # noqa: E731  test/taylorize.jl:2549-2603

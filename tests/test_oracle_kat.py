@@ -179,3 +179,19 @@ def test_trange_matches_step_output_and_nan_fill():
     ok = tr < 1 / 3 - 1e-3
     assert np.all(np.abs(x[ok] - 3 / (1 - 3 * tr[ok])) < 1e-9 * np.abs(x[ok]))
     assert np.isnan(x[-1])
+
+
+def test_events_with_trange_variant():
+    # src/rootfinding.jl:485-584: same events as the (t0, tmax) driver, same in-step outputs as the plain trange
+    # driver; the step that lands on tmax exits before its event test and before nsteps += 1 (547-550)
+    T = 7.019250311844546
+    tape = P.pendulum_tape()
+    tr = np.linspace(0.0, 3 * T, 25)
+    a = oracle.integrate(tape, 28, [1.3, 0.0], kind=L.KIND_EVENTS, trange=tr, abstol=1e-20, maxsteps=1000)
+    b = oracle.integrate(tape, 28, [1.3, 0.0], 0.0, 3 * T, kind=L.KIND_EVENTS, abstol=1e-20, maxsteps=1000)
+    c = oracle.integrate(tape, 28, [1.3, 0.0], trange=tr, abstol=1e-20, maxsteps=1000)
+    assert a.nevents[0] == b.nevents[0] == 5 and np.array_equal(a.tevents[:5], b.tevents[:5])
+    assert np.array_equal(a.xevents[:, :5], b.xevents[:, :5]) and np.array_equal(a.gresids[:5], b.gresids[:5])
+    assert np.array_equal(a.x_trange, c.x_trange) and not np.isnan(a.x_trange).any()
+    assert a.nsteps[0] == c.nsteps[0] == b.nsteps[0] - 1 and a.tfinal[0] == tr[-1]
+    assert np.max(np.abs(a.tevents[:5, 0] - np.arange(1, 6) * T / 2)) < 1e-13  # test/rootfinding.jl:120-122
