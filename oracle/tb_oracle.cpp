@@ -596,10 +596,20 @@ void modifiedGS(const double *A, double *Q, double *R, int n) {
  * lyap_jetcoeffs! 161-211.  State = [q; vec(Phi)] (column-major Phi).          */
 int integ_lyap(Work &w, const double *q0, double t0, double tmax, const tb_opts_t &o, const StepOut *so,
                double *lambda_v /*[dof x stride] or null*/, double *xfinal, double *tfinal, double *lambda,
-               int64_t *nsteps_out, int32_t *status) {
+               int64_t *nsteps_out, int32_t *status, const double *trange = nullptr, int64_t nt = 0,
+               double *xvtr = nullptr /*[dof x nt]*/, double *lamtr = nullptr /*[dof x nt]*/) {
     const tb_ode_desc_t *d = w.d;
     const int dof = d->dof, P = w.P, nx = dof + dof * dof;
     if (!d->has_jac) return TB_ERR_ARG;
+    /* trange variant: src/lyapunovspectrum.jl:481-596 (outputs NaN-prefilled, cache.jl:421-422) */
+    double t1 = 0.0;
+    int64_t iter = 2;
+    if (trange) {
+        t0 = trange[0]; t1 = trange[1]; tmax = trange[nt - 1];
+        const double nan = std::numeric_limits<double>::quiet_NaN();
+        for (int64_t j = 0; j < (int64_t)dof * nt; j++) { xvtr[j] = nan; lamtr[j] = nan; }
+        for (int i = 0; i < dof; i++) { xvtr[(size_t)i * nt] = q0[i]; lamtr[(size_t)i * nt] = 0.0; }
+    }
     std::vector<double> x0(nx, 0.0), jt(dof * dof, 0.0), QH(dof * dof), RH(dof * dof), lsum(dof, 0.0), lam(dof, 0.0);
     for (int i = 0; i < dof; i++) x0[i] = q0[i];
     for (int i = 0; i < dof; i++) jt[i + i * dof] = 1.0;
@@ -664,6 +674,29 @@ int integ_lyap(Work &w, const double *q0, double t0, double tmax, const tb_opts_
         for (int i = 0; i < nx; i++) x0[i] = horner(w.X(i), P, dt);
         for (int i = 0; i < dof * dof; i++) jt[i] = x0[dof + i];
         modifiedGS(jt.data(), QH.data(), RH.data(), dof);
+        if (trange) {
+            /* in-step outputs (lyapunovspectrum.jl:545-558): the state at t1, the exponents from the fundamental
+             * matrix evaluated at the END of the step (the reference evaluates x[dof+ind] at dt, not at t1 - t0), and
+             * the loop test is the reference's literal `t1 < tnext` (no sign factor)                               */
+            const double tnext = t0 + dt;
+            while (t1 < tnext) {
+                for (int i = 0; i < dof; i++) xvtr[(size_t)i * nt + (iter - 1)] = horner(w.X(i), P, t1 - t0);
+                const double tsp = t1 - t00;
+                for (int i = 0; i < dof; i++) lamtr[(size_t)i * nt + (iter - 1)] = (lsum[i] + w.math.log_(RH[i + i * dof])) / tsp;
+                iter += 1;
+                t1 = trange[iter - 1];
+            }
+            if (dt == tmax - t0) {
+                const double tsp = tmax - t00;
+                for (int i = 0; i < dof; i++) {
+                    xvtr[(size_t)i * nt + (iter - 1)] = x0[i];
+                    lam[i] = (lsum[i] + w.math.log_(RH[i + i * dof])) / tsp;
+                    lamtr[(size_t)i * nt + (iter - 1)] = lam[i];
+                }
+                t0 = tnext;
+                break;
+            }
+        }
         t0 += dt;
         double tspan = t0 - t00;
         nsteps += 1;
@@ -768,14 +801,15 @@ int tbo_integrate(const tb_ode_desc_t *d, int order, int kind, int math_mode, in
         Work w(d, order, math_mode, kind == TB_KIND_LYAP ? dof * dof : 0);
         std::vector<double> q(dof), xf(dof), lam(dof);
         std::vector<double> tvl, xvl, psl, lvl, xtr, tev, xev, gre;
-        const bool want_steps = out->tv || out->xv || out->psol || out->lambda_v;
+        const bool want_steps = !trange && (out->tv || out->xv || out->psol || out->lambda_v);
         if (want_steps) {
             tvl.assign(stride, 0.0);
             xvl.assign((size_t)dof * stride, 0.0);
             if (out->psol) psl.assign((size_t)dof * (order + 1) * stride, 0.0);
             if (out->lambda_v) lvl.assign((size_t)dof * stride, 0.0);
         }
-        if (trange) xtr.assign((size_t)dof * nt, 0.0);
+        std::vector<double> ltr;
+        if (trange) { xtr.assign((size_t)dof * nt, 0.0); ltr.assign((size_t)dof * nt, 0.0); }
         if (kind == TB_KIND_EVENTS) { tev.assign(cap, 0.0); xev.assign((size_t)dof * cap, 0.0); gre.assign(cap, 0.0); }
         for (int64_t i = lo; i < hi; i++) {
             for (int c = 0; c < dof; c++) q[c] = q0[(size_t)c * N + i];
@@ -786,7 +820,10 @@ int tbo_integrate(const tb_ode_desc_t *d, int order, int kind, int math_mode, in
             int64_t ns = 0;
             int32_t st = 0, nev = 0;
             int rc = 0;
-            if (trange && kind == TB_KIND_EVENTS)
+            if (trange && kind == TB_KIND_LYAP)
+                rc = integ_lyap(w, q.data(), t0, tmax, o, nullptr, nullptr, xf.data(), &tf, lam.data(), &ns, &st, trange, nt,
+                                xtr.data(), ltr.data());
+            else if (trange && kind == TB_KIND_EVENTS)
                 rc = integ_events(w, q.data(), t0, tmax, o, nullptr, xf.data(), &tf, &ns, &st, tev.data(), xev.data(),
                                   gre.data(), &nev, cap, trange, nt, xtr.data());
             else if (trange) rc = integ_trange(w, q.data(), trange, nt, o, xtr.data(), xf.data(), &tf, &ns, &st);
@@ -796,6 +833,7 @@ int tbo_integrate(const tb_ode_desc_t *d, int order, int kind, int math_mode, in
             else if (kind == TB_KIND_LYAP)
                 rc = integ_lyap(w, q.data(), t0, tmax, o, want_steps ? &so : nullptr,
                                 out->lambda_v ? lvl.data() : nullptr, xf.data(), &tf, lam.data(), &ns, &st);
+
             else rc = integ_plain(w, q.data(), t0, tmax, o, want_steps ? &so : nullptr, xf.data(), &tf, &ns, &st);
             if (rc) { rcs[tid] = rc; return; }
             if (out->xfinal) for (int c = 0; c < dof; c++) out->xfinal[(size_t)c * N + i] = xf[c];
@@ -806,6 +844,9 @@ int tbo_integrate(const tb_ode_desc_t *d, int order, int kind, int math_mode, in
             if (trange && out->xv_trange)
                 for (int c = 0; c < dof; c++)
                     for (int64_t j = 0; j < nt; j++) out->xv_trange[((size_t)c * nt + j) * N + i] = xtr[(size_t)c * nt + j];
+            if (trange && kind == TB_KIND_LYAP && out->lambda_v)
+                for (int c = 0; c < dof; c++)
+                    for (int64_t j = 0; j < nt; j++) out->lambda_v[((size_t)c * nt + j) * N + i] = ltr[(size_t)c * nt + j];
             if (want_steps) {
                 for (int64_t s = 0; s <= ns && s < stride; s++) {
                     if (out->tv) out->tv[(size_t)s * N + i] = tvl[s];

@@ -260,11 +260,14 @@ class EnsembleSolution:
     nevents: Optional[np.ndarray] = None  # [N]
     lam: Optional[np.ndarray] = None      # [dof, N]
     lam_steps: Optional[np.ndarray] = None  # [dof, stride, N]
+    lam_trange: Optional[np.ndarray] = None  # [dof, nt, N]
 
     def trajectory(self, i: int) -> TaylorSolution:
         ns = int(self.nsteps[i])
         if self.x_trange is not None:
             s = TaylorSolution(t=None, x=self.x_trange[:, :, i].T.copy(), status=int(self.status[i]))
+            if self.lam_trange is not None:
+                s.lam = self.lam_trange[:, :, i].T.copy()
             if self.nevents is not None:
                 ne = int(self.nevents[i])
                 s.tevents, s.gresids = self.tevents[:ne, i].copy(), self.gresids[:ne, i].copy()
@@ -313,6 +316,7 @@ def _integrate(tape: Tape, kind: int, q0, t0, tmax, trange, order, abstol, param
         raise ValueError("output must be 'steps' or 'final'")
     kernel_opts = dict(kernel_opts or {})
     wide = bool(kernel_opts.pop("wide", False)) or is_wide(tape)
+    kkind = kind
     if wide:
         if kind != L.KIND_PLAIN:
             raise L.TaylorB200Error("large-state tapes support the plain drivers only (no events / Lyapunov yet)")
@@ -347,6 +351,11 @@ def _integrate(tape: Tape, kind: int, q0, t0, tmax, trange, order, abstol, param
         assert tr.size >= 2 and (np.all(d > 0) or np.all(d < 0)), "trange must be sorted"  # taylorinteg.jl:489,573
         sol.x_trange = np.empty((dof, tr.size, N))
         out.xv_trange = sol.x_trange.ctypes.data_as(L._DP)
+        if kind == L.KIND_LYAP:  # lyap_taylorinteg(f!, q0, trange, ...): exponents at every output time
+            if kkind != L.KIND_LYAPCOL:
+                raise L.TaylorB200Error("the trange variant of lyap_taylorinteg needs the column-parallel kernel")
+            sol.lam_trange, sol.lam = np.empty((dof, tr.size, N)), np.empty((dof, N))
+            out.lambda_v, out.lambda_ = sol.lam_trange.ctypes.data_as(L._DP), sol.lam.ctypes.data_as(L._DP)
         if kind == L.KIND_EVENTS:  # taylorinteg(f!, g, q0, trange, ...): src/rootfinding.jl:440-584
             sol.tevents, sol.gresids = np.zeros((cap, N)), np.zeros((cap, N))
             sol.xevents, sol.nevents = np.zeros((dof, cap, N)), np.zeros(N, dtype=np.int32)
@@ -425,17 +434,25 @@ def taylorinteg_events(tape: Tape, q0, t0, tmax, order, abstol, params=None, tra
     return _integrate(tape, L.KIND_EVENTS, q0, t0, tmax, trange, int(order), abstol, params, **kw)
 
 
-def lyap_taylorinteg(f, q0, t0, tmax, order, abstol, params=None, jacobianfunc=None, *, maxsteps: int = 500,
-                     parse_eqs: bool = True, reltol: float = 0.0, minstepsize: float = 0.0, maxstepsize: float = np.inf,
-                     mode="parity", output=None, kernel_opts=None):
+def lyap_taylorinteg(f, q0, *args, maxsteps: int = 500, parse_eqs: bool = True, reltol: float = 0.0,
+                     minstepsize: float = 0.0, maxstepsize: float = np.inf, mode="parity", output=None, kernel_opts=None):
     """Lyapunov spectrum (src/lyapunovspectrum.jl:293-429).  The Jacobian always comes from first-order forward
     mode on the tape (the reference's TaylorN path); `jacobianfunc` is accepted and ignored, since the reference
     requires both to agree (test/lyapunov.jl:294-296)."""
+    # (q0, t0, tmax, order, abstol[, params[, jacobianfunc]])  or  (q0, trange, order, abstol[, params[, jacobianfunc]])
+    trange = None
+    if len(args) >= 1 and np.ndim(args[0]) >= 1:  # src/lyapunovspectrum.jl:431-596
+        trange, order, abstol = args[:3]
+        params = args[3] if len(args) > 3 else None
+        t0 = tmax = None
+    else:
+        t0, tmax, order, abstol = args[:4]
+        params = args[4] if len(args) > 4 else None
     dof = np.asarray(q0).shape[0]
     tape = _as_tape(f, dof, params, jacobian=True)
     if tape.jac is None:
         raise ValueError("the tape has no Jacobian; build it with taylorize(..., jacobian=True)")
-    return _integrate(tape, L.KIND_LYAP, q0, t0, tmax, None, int(order), abstol, params, maxsteps=maxsteps, dense=False,
+    return _integrate(tape, L.KIND_LYAP, q0, t0, tmax, trange, int(order), abstol, params, maxsteps=maxsteps, dense=False,
                       reltol=reltol, minstepsize=minstepsize, maxstepsize=maxstepsize, mode=mode, output=output,
                       kernel_opts=kernel_opts)
 

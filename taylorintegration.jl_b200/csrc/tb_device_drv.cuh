@@ -724,11 +724,27 @@ __device__ __forceinline__ bool tb_traj_init(TbTraj &T, double *__restrict__ smt
     T.nsteps = 1;
     T.st = 0;
     T.iter = 2;
-    T.t0 = a.t0;
-    T.tmax = a.tmax;
-    T.t1 = 0.0;
+    if (a.trange) { /* src/lyapunovspectrum.jl:504-515; xv and lambda NaN-prefilled (cache.jl:421-422) */
+        T.t0 = a.trange[0];
+        T.t1 = a.trange[1];
+        T.tmax = a.trange[a.nt - 1];
+        if (a.xv_trange && T.lit == 0)
+            for (int c = 0; c < TB_NQ; c++) {
+                a.xv_trange[((long long)c * a.nt) * N + i] = T.x0[c];
+                for (long long j = 1; j < a.nt; j++) a.xv_trange[((long long)c * a.nt + j) * N + i] = TB_NAN;
+            }
+        if (a.lambda_v) {
+            a.lambda_v[((long long)T.lit * a.nt) * N + i] = 0.0;
+            for (long long j = 1; j < a.nt; j++) a.lambda_v[((long long)T.lit * a.nt + j) * N + i] = TB_NAN;
+        }
+    } else {
+        T.t0 = a.t0;
+        T.tmax = a.tmax;
+        T.t1 = 0.0;
+    }
     T.sign = copysign(1.0, B_(T.tmax, T.t0));
     T.t00 = T.t0;
+    if (a.trange) return !(M_(T.sign, T.t0) < M_(T.sign, T.tmax));
     if (T.lit == 0) {
         if (a.tv) a.tv[i] = T.t0;
         if (a.xv)
@@ -762,13 +778,42 @@ __device__ __forceinline__ bool tb_traj_step(TbTraj &T, double *__restrict__ smt
 #pragma unroll
         for (int r = 0; r < TB_NQ; r++) A[r + j * TB_NQ] = __shfl_sync(T.tmask, xn[TB_NQ + r], T.leader + j);
     tb_mgs(A, QH, Rd);
-    T.t0 = A_(T.t0, dt);
-    const double tspan = B_(T.t0, T.t00);
-    T.nsteps += 1;
     double rd = Rd[0];
 #pragma unroll
     for (int j = 1; j < TB_NQ; j++) rd = (T.lit == j) ? Rd[j] : rd;
-    T.lsum = A_(T.lsum, tb_log(rd));
+    const double lr = tb_log(rd);
+    if (a.trange) {
+        /* in-step outputs of the trange variant, src/lyapunovspectrum.jl:545-571: states at t1, exponents from the
+         * end-of-step fundamental matrix, the reference's literal `t1 < tnext` test; the step that lands on tmax
+         * stores its end point and leaves the loop                                                             */
+        const double tnext = A_(T.t0, dt);
+        const long long N = a.N;
+        while (T.t1 < tnext) {
+            const double d1 = B_(T.t1, T.t0);
+            if (a.xv_trange && T.lit == 0) {
+                TB_UNROLL_V2
+                for (int c = 0; c < TB_NQ; c++)
+                    a.xv_trange[((long long)c * a.nt + (T.iter - 1)) * N + T.i] = TB_HORNER(c, d1);
+            }
+            if (a.lambda_v) a.lambda_v[((long long)T.lit * a.nt + (T.iter - 1)) * N + T.i] = D_(A_(T.lsum, lr), B_(T.t1, T.t00));
+            T.iter += 1;
+            T.t1 = a.trange[T.iter - 1];
+        }
+        if (dt == B_(T.tmax, T.t0)) {
+            T.lam = D_(A_(T.lsum, lr), B_(T.tmax, T.t00));
+            if (a.xv_trange && T.lit == 0)
+                for (int c = 0; c < TB_NQ; c++) a.xv_trange[((long long)c * a.nt + (T.iter - 1)) * N + T.i] = xn[c];
+            if (a.lambda_v) a.lambda_v[((long long)T.lit * a.nt + (T.iter - 1)) * N + T.i] = T.lam;
+#pragma unroll
+            for (int c = 0; c < TB_NQ; c++) T.x0[c] = xn[c];
+            T.t0 = tnext;
+            return true;
+        }
+    }
+    T.t0 = A_(T.t0, dt);
+    const double tspan = B_(T.t0, T.t00);
+    T.nsteps += 1;
+    T.lsum = A_(T.lsum, lr);
     T.lam = D_(T.lsum, tspan);
     {
         const long long s = T.nsteps - 1, N = a.N;
@@ -779,7 +824,7 @@ __device__ __forceinline__ bool tb_traj_step(TbTraj &T, double *__restrict__ smt
 #pragma unroll
                 for (int c = 0; c < TB_NQ; c++) a.xv[((long long)c * a.stride + s) * N + T.i] = xn[c];
         }
-        if (a.lambda_v && st_ok) a.lambda_v[((long long)T.lit * a.stride + s) * N + T.i] = T.lam;
+        if (a.lambda_v && st_ok && !a.trange) a.lambda_v[((long long)T.lit * a.stride + s) * N + T.i] = T.lam;
     }
 #pragma unroll
     for (int c = 0; c < TB_NQ; c++) T.x0[c] = xn[c];

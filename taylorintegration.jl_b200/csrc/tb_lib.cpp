@@ -344,7 +344,7 @@ static int integrate_host(tb_kernel *k, int64_t N, const double *q0, const doubl
                           const double *trange, int64_t nt, const tb_opts_t *opts, tb_out_t *out) {
     if (!k || !opts || !out || N < 0 || !q0) { set_error("tb_integrate: bad argument"); return TB_ERR_ARG; }
     if (trange && nt < 2) { set_error("tb_integrate_trange: trange needs at least two points"); return TB_ERR_ARG; }
-    if (trange && k->co.kind != TB_KIND_PLAIN && k->co.kind != TB_KIND_EVENTS) { set_error("trange is implemented for TB_KIND_PLAIN and TB_KIND_EVENTS kernels"); return TB_ERR_UNSUPPORTED; }
+    if (trange && k->co.kind == TB_KIND_LYAP) { set_error("trange is implemented for TB_KIND_PLAIN, TB_KIND_EVENTS and TB_KIND_LYAPCOL kernels"); return TB_ERR_UNSUPPORTED; }
     const tb_ode_desc_t &d = k->ode.desc;
     if (d.npar > 0 && !params) { set_error("tb_integrate: params is NULL"); return TB_ERR_ARG; }
     if (k->co.kind == TB_KIND_EVENTS && opts->eventorder > k->co.order) { set_error("order must be >= eventorder (rootfinding.jl:321)"); return TB_ERR_ARG; }
@@ -382,6 +382,7 @@ static int integrate_host(tb_kernel *k, int64_t N, const double *q0, const doubl
     if (k->co.kind == TB_KIND_LYAP || lyapcol) {
         want(out->lambda, (void **)&dv.lambda, dof * n * 8);
         if (!trange) want(out->lambda_v, (void **)&dv.lambda_v, dof * stride * n * 8);
+        else want(out->lambda_v, (void **)&dv.lambda_v, dof * (size_t)nt * n * 8); /* exponents at trange, [dof x nt x N] */
     }
     size_t total = rup(256) + rup(dof * n * 8) + rup(npar_elems * 8) + rup((size_t)(trange ? nt : 0) * 8);
     for (auto &it : outs) total += rup(it.bytes);
@@ -621,7 +622,7 @@ int tb_integrate_device(tb_kernel_t *k, int64_t N, const double *d_q0, const dou
                         const double *d_trange, int64_t nt, const tb_opts_t *opts, const tb_out_t *d_out, void *d_work,
                         void *stream) {
     if (!k || !opts || !d_out || !d_work || N < 0) { set_error("tb_integrate_device: bad argument"); return TB_ERR_ARG; }
-    if (d_trange && k->co.kind != TB_KIND_PLAIN && k->co.kind != TB_KIND_EVENTS) { set_error("trange is implemented for TB_KIND_PLAIN and TB_KIND_EVENTS kernels"); return TB_ERR_UNSUPPORTED; }
+    if (d_trange && k->co.kind == TB_KIND_LYAP) { set_error("trange is implemented for TB_KIND_PLAIN, TB_KIND_EVENTS and TB_KIND_LYAPCOL kernels"); return TB_ERR_UNSUPPORTED; }
     if (N == 0) return TB_OK;
     Loaded *l = nullptr;
     int rc = ensure_loaded(k, &l);

@@ -112,6 +112,9 @@ def integrate(tape: tb.Tape, order: int, q0, t0=0.0, tmax=None, params=None, *, 
         sol.x_trange = np.zeros((dof, tr.size, N))
         out.xv_trange = sol.x_trange.ctypes.data_as(L._DP)
         t0, tmax = tr[0], tr[-1]
+        if kind == L.KIND_LYAP:
+            sol.lam_trange = np.zeros((dof, tr.size, N))
+            out.lambda_v = sol.lam_trange.ctypes.data_as(L._DP)
     elif steps:
         sol.t, sol.x = np.zeros((stride, N)), np.zeros((dof, stride, N))
         out.tv, out.xv = sol.t.ctypes.data_as(L._DP), sol.x.ctypes.data_as(L._DP)

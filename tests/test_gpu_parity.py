@@ -180,6 +180,20 @@ def test_lorenz_lyapunov():
     assert np.max(np.abs(f.lam[-1] - lam)) < 1e-4
 
 
+def test_lyapunov_trange_variant():
+    # lyap_taylorinteg(f!, q0, trange, ...): src/lyapunovspectrum.jl:431-596
+    tape = P.lorenz_tape()
+    tr = np.linspace(0.0, 2.0, 41)
+    q0, pars = P.lorenz_ensemble(23)
+    g = tb.lyap_taylorinteg(tape, q0, tr, 28, 1e-20, pars, maxsteps=2000)
+    o = oracle.integrate(tape, 28, q0, params=pars, kind=L.KIND_LYAP, trange=tr, maxsteps=2000, nthreads=8)
+    assert np.array_equal(g.x_trange, o.x_trange) and np.array_equal(g.lam_trange, o.lam_trange)
+    assert np.array_equal(g.lam, o.lam) and np.array_equal(g.nsteps, o.nsteps) and np.array_equal(g.xfinal, o.xfinal)
+    one = tb.lyap_taylorinteg(tape, np.array([19.0, 20.0, 50.0]), tr, 28, 1e-20, np.array([16.0, 45.92, 4.0]), maxsteps=2000)
+    assert one.x.shape == (41, 3) and one.lam.shape == (41, 3) and not np.isnan(one.lam).any()
+    assert abs(one.lam[-1].sum() + 21.0) < 1e-9
+
+
 def test_lyapunov_column_tape_structure():
     from taylorintegration_b200.tape import lyap_column_tape
     col = lyap_column_tape(P.lorenz_tape())

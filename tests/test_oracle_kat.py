@@ -195,3 +195,19 @@ def test_events_with_trange_variant():
     assert np.array_equal(a.x_trange, c.x_trange) and not np.isnan(a.x_trange).any()
     assert a.nsteps[0] == c.nsteps[0] == b.nsteps[0] - 1 and a.tfinal[0] == tr[-1]
     assert np.max(np.abs(a.tevents[:5, 0] - np.arange(1, 6) * T / 2)) < 1e-13  # test/rootfinding.jl:120-122
+
+
+def test_lyapunov_trange_variant():
+    # src/lyapunovspectrum.jl:481-596: states and exponents at the output times (NaN-prefilled, first column q0 / 0);
+    # the last column carries the exponents of the (t0, tmax) driver at tmax, and the orbit is the plain trange orbit
+    tape = P.lorenz_tape()
+    par = [16.0, 45.92, 4.0]
+    tr = np.linspace(0.0, 2.0, 41)
+    a = oracle.integrate(tape, 28, [19.0, 20.0, 50.0], params=par, kind=L.KIND_LYAP, trange=tr, maxsteps=2000)
+    b = oracle.integrate(tape, 28, [19.0, 20.0, 50.0], 0.0, 2.0, par, kind=L.KIND_LYAP, maxsteps=2000)
+    c = oracle.integrate(P.lorenz_tape(jacobian=False), 28, [19.0, 20.0, 50.0], params=par, trange=tr, maxsteps=2000)
+    lam_tr = a.lam_trange if getattr(a, "lam_trange", None) is not None else a.lam_steps
+    assert np.array_equal(a.x_trange, c.x_trange) and not np.isnan(a.x_trange).any()
+    assert np.array_equal(lam_tr[:, 0, 0], np.zeros(3)) and not np.isnan(lam_tr).any()
+    assert np.array_equal(lam_tr[:, -1, 0], b.lam[:, 0]) and np.array_equal(a.lam[:, 0], b.lam[:, 0])
+    assert abs(lam_tr[:, -1, 0].sum() + 21.0) < 1e-9 and a.nsteps[0] == b.nsteps[0] - 1
