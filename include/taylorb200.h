@@ -275,7 +275,10 @@ const void *tb_kernel_cubin(const tb_kernel_t *k, size_t *nbytes);
  * q0 [dof x N]; params [npar x N] or [npar]; t0/tmax scalars.               */
 int tb_integrate(tb_kernel_t *k, int64_t N, const double *q0, const double *params,
                  double t0, double tmax, const tb_opts_t *opts, tb_out_t *out);
-/* same with a sorted output grid trange[nt] shared by all trajectories      */
+/* same with a sorted output grid trange[nt] shared by all trajectories (states in out->xv_trange [dof x nt x N],
+ * NaN-prefilled like the reference's caches).  Replaces taylorinteg.jl:582-642 (TB_KIND_PLAIN), rootfinding.jl:485-584
+ * (TB_KIND_EVENTS: events as in tb_integrate) and lyapunovspectrum.jl:481-596 (TB_KIND_LYAPCOL: out->lambda_v then
+ * holds the exponents at the output times, [dof x nt x N], out->lambda the ones at trange[nt-1]).                     */
 int tb_integrate_trange(tb_kernel_t *k, int64_t N, const double *q0, const double *params,
                         const double *trange, int64_t nt, const tb_opts_t *opts, tb_out_t *out);
 
