@@ -774,6 +774,11 @@ int generate_unrolled(const Ode &ode, const tb_compile_opts_t &co, Layout &L, st
         if (d.dof < 2 || (d.dof & 1) || d.dof / 2 > 16) { err = "TB_KIND_LYAPCOL needs the column system [x; v] (an even number of components, at most 32)"; return TB_ERR_ARG; }
     } else if (co.kind != TB_KIND_PLAIN) { err = "the unrolled generator covers TB_KIND_PLAIN, TB_KIND_EVENTS and TB_KIND_LYAPCOL"; return TB_ERR_UNSUPPORTED; }
     if (co.order < 1 || co.order > 40) { err = "order must be in 1..40 for the unrolled generator"; return TB_ERR_UNSUPPORTED; }
+    if ((co.flags & 128) && co.kind != TB_KIND_PLAIN) {
+        /* the per-order barriers sit inside the jet body, which the event and team kernels also call from divergent code */
+        err = "TB_CF_BLOCK_LOCKSTEP is available for TB_KIND_PLAIN kernels only";
+        return TB_ERR_ARG;
+    }
     if (d.dof > 16 || d.nops > 200) { err = "tape too large to unroll"; return TB_ERR_UNSUPPORTED; }
     std::set<int32_t> seen;
     for (int j = 0; j < d.nops; j++) {
@@ -831,7 +836,11 @@ int generate_unrolled(const Ode &ode, const tb_compile_opts_t &co, Layout &L, st
     if (co.kind == TB_KIND_LYAPCOL) e.line("#define TB_NQ %d", d.dof / 2);
     e.line("#define TB_EV_NOPS 0");
     e.line("#define TB_JAC_NOPS 0");
-    e.line("#define TB_BAR %d", (co.flags & 128) ? 1 : (co.flags & 1024) ? 2 : 0);
+    /* step lockstep (one block barrier per step) is the default for event kernels: their step body is long and
+     * branchy relative to its FP64 work, and sharing instruction fetches is worth 19 % on the pendulum workload;
+     * the plain Kepler kernel gains nothing from it (+-1 %), so it stays opt-in there (TB_CF_STEP_LOCKSTEP)   */
+    const bool step_lock = (co.flags & 1024) || (co.kind == TB_KIND_EVENTS && !(co.flags & 16384));
+    e.line("#define TB_BAR %d", (co.flags & 128) ? 1 : step_lock ? 2 : 0);
     e.s += embedded_math_h();
     e.s += embedded_device_pre();
     e.line("/* placement: %d series in registers, %d in shared memory */", g.nreg, g.nsm);

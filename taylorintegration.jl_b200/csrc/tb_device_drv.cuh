@@ -871,7 +871,11 @@ extern "C" __global__ void __launch_bounds__(TB_BT, TB_MINB) tb_ensemble_kernel(
             have = true;
             if (tb_traj_init(T, smt, a, i)) { tb_traj_finish(T, a); have = false; }
         }
+#if TB_BAR == 2
+        if (!__syncthreads_or(have)) break; /* step lockstep: the warps of the block share the instruction stream */
+#else
         if (!__any_sync(full, have)) break;
+#endif
         if (have) {
             if (tb_traj_step(T, smt, a, true)) { tb_traj_finish(T, a); have = false; }
         }
