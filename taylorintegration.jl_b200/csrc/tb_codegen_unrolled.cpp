@@ -836,6 +836,8 @@ int generate_unrolled(const Ode &ode, const tb_compile_opts_t &co, Layout &L, st
     if (co.kind == TB_KIND_LYAPCOL) e.line("#define TB_NQ %d", d.dof / 2);
     e.line("#define TB_EV_NOPS 0");
     e.line("#define TB_JAC_NOPS 0");
+    /* opt-in only: measured -7 % on Kepler-28 (4 register series) and -3 % on pendulum-25 (3 register series) */
+    e.line("#define TB_STEPSIZE_PAIR %d", (parity && (co.flags & 65536)) ? 1 : 0);
     /* step lockstep (one block barrier per step) is the default for event kernels: their step body is long and
      * branchy relative to its FP64 work, and sharing instruction fetches is worth 19 % on the pendulum workload;
      * the plain Kepler kernel gains nothing from it (+-1 %), so it stays opt-in there (TB_CF_STEP_LOCKSTEP)   */

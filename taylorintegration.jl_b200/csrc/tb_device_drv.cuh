@@ -33,8 +33,18 @@ __device__ __noinline__ double tb_stepsize_k(double a, double eps, int k) {
     return tb_pow(aux, kinv);
 }
 
-/* NOTE (round 1, measured): evaluating the two step-size powers in one interleaved body (tb_pow_pair, tb_math.h)
- * costs 7 % on Kepler-28: the jets occupy ~232 registers across the call, and the wider callee spills. */
+#ifndef TB_STEPSIZE_PAIR
+#define TB_STEPSIZE_PAIR 0
+#endif
+#if TB_STEPSIZE_PAIR
+/* (eps/a1)^(1/(P-1)) and (eps/a2)^(1/P) together: same bits as two tb_stepsize_k calls (1/k is the same correctly
+ * rounded quotient, folded at compile time).  Measured: -7 % on Kepler-28 parity (232 registers of jets live across
+ * the call, the wider callee spills) and -3 % on pendulum-25: the other warps already cover the latency.  Opt-in. */
+__device__ __noinline__ tb_pair tb_stepsize_pair(double a1, double a2, double eps) {
+    const double x1 = D_(eps, a1), x2 = D_(eps, a2);
+    return tb_pow_pair(x1, 1.0 / (double)(TB_P - 1), x2, 1.0 / (double)TB_P);
+}
+#endif
 
 #if TB_VARIANT == 1
 /* evaluate(a::Taylor1, dt): Horner, s = a[P]; s = s*dt + a[k]  (TaylorSeries) */
@@ -159,13 +169,32 @@ __device__ __forceinline__ double tb_u_stepsize(const TbJets &J, const double *_
          * components within 2^-40 of the maximum are evaluated as well: same bits as the
          * reference's loop over all components (stepsize.jl:83-86), 2 pow calls instead of 2*dof.
          * NaN coefficients drop out of fmax here exactly as they drop out of min there.       */
+#if TB_STEPSIZE_PAIR
+        /* TB_CF_PAIR_POW: the two powers in ONE straight-line body (tb_pow_pair, same bits) so that their dependent
+         * chains overlap; measured slower than two calls on both benchmark kernels, kept as an option            */
+        double mk2[2];
+#pragma unroll
+        for (int j = 0; j < 2; j++) {
+            mk2[j] = 0.0;
+#pragma unroll
+            for (int c = 0; c < TB_NQ; c++) mk2[j] = fmax(mk2[j], fabs(TB_X(c, TB_P - 1 + j)));
+        }
+        const bool both = mk2[0] != 0.0 && mk2[1] != 0.0;
+        tb_pair hp;
+        hp.a = 0.0; hp.b = 0.0;
+        if (both) hp = tb_stepsize_pair(mk2[0], mk2[1], a.abstol);
+#endif
 #pragma unroll
         for (int k = TB_P - 1; k <= TB_P; k++) {
             double m = 0.0, ac[TB_NQ];
 #pragma unroll
             for (int c = 0; c < TB_NQ; c++) { ac[c] = fabs(TB_X(c, k)); m = fmax(m, ac[c]); }
             if (m != 0.0) {
+#if TB_STEPSIZE_PAIR
+                double hk = both ? (k == TB_P ? hp.b : hp.a) : tb_stepsize_k(m, a.abstol, k);
+#else
                 double hk = tb_stepsize_k(m, a.abstol, k);
+#endif
                 const double thr = M_(m, 0.99999999999909051);
 #pragma unroll
                 for (int c = 0; c < TB_NQ; c++)
