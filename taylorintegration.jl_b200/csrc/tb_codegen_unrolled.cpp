@@ -863,6 +863,10 @@ int generate_unrolled(const Ode &ode, const tb_compile_opts_t &co, Layout &L, st
         const char *cmp[] = {"", ">", "<", ">=", "<="};
         if (d.ev_gate_cmp == TB_GATE_ALWAYS) e.line("#define TB_EV_GATE_EXPR true");
         else e.line("#define TB_EV_GATE_EXPR (tb_u_x(J, smt, x0, %d, 0) %s 0.0)", TB_OPERAND_INDEX(d.ev_gate), cmp[d.ev_gate_cmp]);
+        /* order-0 forms on the state alone: what tb_traj_init needs when eventorder == 0 (no jets at refill) */
+        e.line("#define TB_EV_G0(x0) ((x0)[%d])", cg);
+        if (d.ev_gate_cmp == TB_GATE_ALWAYS) e.line("#define TB_EV_GATE0(x0) true");
+        else e.line("#define TB_EV_GATE0(x0) ((x0)[%d] %s 0.0)", TB_OPERAND_INDEX(d.ev_gate), cmp[d.ev_gate_cmp]);
         e.line("/* coefficient k (run-time) of g = x[%d] */", cg);
         e.line("__device__ __forceinline__ double tb_u_gcoef(const TbJets &J, const double *__restrict__ smt, const double *__restrict__ x0, const int k) {");
         e.line("  switch (k) {");

@@ -406,7 +406,12 @@ __device__ __forceinline__ bool tb_traj_init(TbTraj &T, double *__restrict__ smt
     T.f_old = tb_eval_event(smt, T.par, T.t0);
     T.g_old = TB_EV_G(a.eventorder);
 #else
-    { /* variant 2: g is a state component (generated accessors), jets in registers / shared memory */
+    if (a.eventorder == 0) {
+        /* g and the gate are state components: their order-0 coefficients are the state itself, so a lane that
+         * refills needs no jet evaluation (which would stall the other warps of a step-lockstep block)          */
+        T.f_old = TB_EV_GATE0(T.x0);
+        T.g_old = TB_EV_G0(T.x0);
+    } else { /* variant 2: g is a state component (generated accessors), jets in registers / shared memory */
         TbJets J;
         const double *x0 = T.x0;
         tb_u_jets(J, smt, T.par, T.t0, x0);
