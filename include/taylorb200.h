@@ -200,6 +200,7 @@ typedef struct tb_compile_opts {
 #define TB_CF_SPLIT 8192        /* registers hold the low coefficients of every recurrence-read series, shared memory the high ones */
 #define TB_CF_NO_STEP_LOCKSTEP 16384 /* event kernels: no block barrier per step (it is their default) */
 #define TB_CF_PAIR_POW 65536     /* parity: evaluate the two step-size powers in one interleaved body (measured slower) */
+#define TB_CF_LYAP_TRANGE 131072  /* TB_KIND_LYAPCOL: build the trange variant (tb_integrate_trange needs it) */
 #define TB_CF_SYNC_EVERY4 2048   /* with TB_CF_BLOCK_LOCKSTEP: barrier every 4th order only */
 
 /* ---- integration options: keyword arguments of taylorinteg -------------- */

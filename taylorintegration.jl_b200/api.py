@@ -333,6 +333,8 @@ def _integrate(tape: Tape, kind: int, q0, t0, tmax, trange, order, abstol, param
             col = _column_tape(tape)
             if col is not None:
                 ktape, kkind = col, L.KIND_LYAPCOL
+                if trange is not None:  # the trange variant is a separate build of the kernel (TB_CF_LYAP_TRANGE)
+                    kernel_opts["flags"] = int(kernel_opts.get("flags", 0)) | 131072
         k = get_kernel(ktape, int(order), kkind, _mode(mode), **(kernel_opts or {}))
     cap = int(event_capacity) if event_capacity else int(maxsteps) + 1
     o = make_opts(abstol, reltol, minstepsize, maxstepsize, maxsteps, eventorder, newtoniter, nrabstol, cap, per)

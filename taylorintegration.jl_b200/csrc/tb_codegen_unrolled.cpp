@@ -834,6 +834,7 @@ int generate_unrolled(const Ode &ode, const tb_compile_opts_t &co, Layout &L, st
     e.line("#define TB_MODE %d", co.mode);
     e.line("#define TB_KIND %d", co.kind);
     if (co.kind == TB_KIND_LYAPCOL) e.line("#define TB_NQ %d", d.dof / 2);
+    if (co.kind == TB_KIND_LYAPCOL) e.line("#define TB_LYAP_TRANGE %d", (co.flags & 131072) ? 1 : 0);
     e.line("#define TB_EV_NOPS 0");
     e.line("#define TB_JAC_NOPS 0");
     /* opt-in only: measured -7 % on Kepler-28 (4 register series) and -3 % on pendulum-25 (3 register series) */

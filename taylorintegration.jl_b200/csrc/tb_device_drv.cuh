@@ -24,6 +24,9 @@
 #ifndef TB_NQ
 #define TB_NQ TB_DOF
 #endif
+#ifndef TB_LYAP_TRANGE
+#define TB_LYAP_TRANGE 0
+#endif
 
 /* _stepsize: src/integrator/stepsize.jl:107-111   (eps/a)^(1/k).  Not inlined: the
  * double-double pow is ~300 instructions and is called 2*dof times per step.    */
@@ -758,7 +761,11 @@ __device__ __forceinline__ bool tb_traj_init(TbTraj &T, double *__restrict__ smt
     T.nsteps = 1;
     T.st = 0;
     T.iter = 2;
+#if !TB_LYAP_TRANGE
+    if (false) {
+#else
     if (a.trange) { /* src/lyapunovspectrum.jl:504-515; xv and lambda NaN-prefilled (cache.jl:421-422) */
+#endif
         T.t0 = a.trange[0];
         T.t1 = a.trange[1];
         T.tmax = a.trange[a.nt - 1];
@@ -778,7 +785,9 @@ __device__ __forceinline__ bool tb_traj_init(TbTraj &T, double *__restrict__ smt
     }
     T.sign = copysign(1.0, B_(T.tmax, T.t0));
     T.t00 = T.t0;
+#if TB_LYAP_TRANGE
     if (a.trange) return !(M_(T.sign, T.t0) < M_(T.sign, T.tmax));
+#endif
     if (T.lit == 0) {
         if (a.tv) a.tv[i] = T.t0;
         if (a.xv)
@@ -816,6 +825,8 @@ __device__ __forceinline__ bool tb_traj_step(TbTraj &T, double *__restrict__ smt
 #pragma unroll
     for (int j = 1; j < TB_NQ; j++) rd = (T.lit == j) ? Rd[j] : rd;
     const double lr = tb_log(rd);
+#if TB_LYAP_TRANGE /* compiled in only for kernels built with TB_CF_LYAP_TRANGE: the extra live values cost the
+                    * (t0, tmax) driver 6 % on Lorenz-28 */
     if (a.trange) {
         /* in-step outputs of the trange variant, src/lyapunovspectrum.jl:545-571: states at t1, exponents from the
          * end-of-step fundamental matrix, the reference's literal `t1 < tnext` test; the step that lands on tmax
@@ -844,6 +855,7 @@ __device__ __forceinline__ bool tb_traj_step(TbTraj &T, double *__restrict__ smt
             return true;
         }
     }
+#endif
     T.t0 = A_(T.t0, dt);
     const double tspan = B_(T.t0, T.t00);
     T.nsteps += 1;
@@ -858,7 +870,12 @@ __device__ __forceinline__ bool tb_traj_step(TbTraj &T, double *__restrict__ smt
 #pragma unroll
                 for (int c = 0; c < TB_NQ; c++) a.xv[((long long)c * a.stride + s) * N + T.i] = xn[c];
         }
-        if (a.lambda_v && st_ok && !a.trange) a.lambda_v[((long long)T.lit * a.stride + s) * N + T.i] = T.lam;
+#if TB_LYAP_TRANGE
+        const bool per_step = !a.trange; /* in the trange variant lambda_v has the [dof x nt x N] layout */
+#else
+        const bool per_step = true;
+#endif
+        if (a.lambda_v && st_ok && per_step) a.lambda_v[((long long)T.lit * a.stride + s) * N + T.i] = T.lam;
     }
 #pragma unroll
     for (int c = 0; c < TB_NQ; c++) T.x0[c] = xn[c];

@@ -353,6 +353,10 @@ static int integrate_host(tb_kernel *k, int64_t N, const double *q0, const doubl
     int rc = ensure_loaded(k, &l);
     if (rc) return rc;
     const bool lyapcol = k->co.kind == TB_KIND_LYAPCOL;
+    if (lyapcol && (trange != nullptr) != ((k->co.flags & TB_CF_LYAP_TRANGE) != 0)) {
+        set_error("TB_KIND_LYAPCOL: kernels built with TB_CF_LYAP_TRANGE serve tb_integrate_trange, the others tb_integrate");
+        return TB_ERR_ARG;
+    }
     const size_t dof = lyapcol ? d.dof / 2 : d.dof, n = (size_t)N, np1 = k->co.order + 1;
     if (lyapcol && out->psol) { set_error("TB_KIND_LYAPCOL has no dense output"); return TB_ERR_UNSUPPORTED; }
     const size_t stride = opts->steps_stride ? opts->steps_stride : opts->maxsteps + 1;
