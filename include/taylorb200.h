@@ -201,6 +201,7 @@ typedef struct tb_compile_opts {
 #define TB_CF_NO_STEP_LOCKSTEP 16384 /* event kernels: no block barrier per step (it is their default) */
 #define TB_CF_PAIR_POW 65536     /* parity: evaluate the two step-size powers in one interleaved body (measured slower) */
 #define TB_CF_LYAP_TRANGE 131072  /* TB_KIND_LYAPCOL: build the trange variant (tb_integrate_trange needs it) */
+#define TB_CF_FINAL_ONLY 262144   /* TB_KIND_PLAIN: final-state outputs only (no trange, tv/xv, psol) */
 #define TB_CF_SYNC_EVERY4 2048   /* with TB_CF_BLOCK_LOCKSTEP: barrier every 4th order only */
 
 /* ---- integration options: keyword arguments of taylorinteg -------------- */

@@ -335,6 +335,9 @@ def _integrate(tape: Tape, kind: int, q0, t0, tmax, trange, order, abstol, param
                 ktape, kkind = col, L.KIND_LYAPCOL
                 if trange is not None:  # the trange variant is a separate build of the kernel (TB_CF_LYAP_TRANGE)
                     kernel_opts["flags"] = int(kernel_opts.get("flags", 0)) | 131072
+        if kind == L.KIND_PLAIN and trange is None and output == "final" and not kernel_opts.pop("full_outputs", False):
+            # final states only: the build without output code in the step body (TB_CF_FINAL_ONLY), +4 % on Kepler-28
+            kernel_opts["flags"] = int(kernel_opts.get("flags", 0)) | 262144
         k = get_kernel(ktape, int(order), kkind, _mode(mode), **(kernel_opts or {}))
     cap = int(event_capacity) if event_capacity else int(maxsteps) + 1
     o = make_opts(abstol, reltol, minstepsize, maxstepsize, maxsteps, eventorder, newtoniter, nrabstol, cap, per)

@@ -833,6 +833,7 @@ int generate_unrolled(const Ode &ode, const tb_compile_opts_t &co, Layout &L, st
     e.line("#define TB_MINB 1");
     e.line("#define TB_MODE %d", co.mode);
     e.line("#define TB_KIND %d", co.kind);
+    if (co.kind == TB_KIND_PLAIN || co.kind == TB_KIND_EVENTS) e.line("#define TB_FINAL_ONLY %d", (co.flags & 262144) ? 1 : 0);
     if (co.kind == TB_KIND_LYAPCOL) e.line("#define TB_NQ %d", d.dof / 2);
     if (co.kind == TB_KIND_LYAPCOL) e.line("#define TB_LYAP_TRANGE %d", (co.flags & 131072) ? 1 : 0);
     e.line("#define TB_EV_NOPS 0");

@@ -27,6 +27,9 @@
 #ifndef TB_LYAP_TRANGE
 #define TB_LYAP_TRANGE 0
 #endif
+#ifndef TB_FINAL_ONLY
+#define TB_FINAL_ONLY 0
+#endif
 
 /* _stepsize: src/integrator/stepsize.jl:107-111   (eps/a)^(1/k).  Not inlined: the
  * double-double pow is ~300 instructions and is called 2*dof times per step.    */
@@ -490,6 +493,16 @@ __device__ __forceinline__ bool tb_traj_step(TbTraj &T, double *__restrict__ smt
     double xn[TB_DOF];
 #pragma unroll
     for (int c = 0; c < TB_DOF; c++) xn[c] = TB_HORNER(c, dt);
+#if TB_FINAL_ONLY
+    /* final-state build (TB_CF_FINAL_ONLY): no output grid, no per-step or dense output in the step body; the host
+     * refuses such requests for this kernel.  Code that is only disabled at run time still costs the jets' scheduler
+     * registers (measured on the Lorenz column kernel: 6 %).                                                     */
+#pragma unroll
+    for (int c = 0; c < TB_DOF; c++) T.x0[c] = xn[c];
+    T.t0 = A_(T.t0, dt);
+    tb_update_cache(smt, T.x0);
+    T.nsteps += 1;
+#else
     if (a.trange) {
         const double tnext = A_(T.t0, dt);
         const long long N = a.N;
@@ -523,6 +536,7 @@ __device__ __forceinline__ bool tb_traj_step(TbTraj &T, double *__restrict__ smt
         T.nsteps += 1;
         tb_store_step(T, smt, a);
     }
+#endif /* TB_FINAL_ONLY */
     if (T.nsteps > a.maxsteps) { T.st |= TB_ST_MAXSTEPS; return true; }
     if (!tb_isfinite_state(T.x0)) { T.st |= TB_ST_NONFINITE; return true; }
     return !(M_(T.sign, T.t0) < M_(T.sign, T.tmax));
@@ -538,6 +552,7 @@ __device__ __forceinline__ bool tb_traj_step(TbTraj &T, double *__restrict__ smt
     double xn[TB_DOF];
 #pragma unroll
     for (int c = 0; c < TB_DOF; c++) xn[c] = TB_HORNER(c, dt);
+#if !TB_FINAL_ONLY
     if (a.trange) {
         /* the trange variant with events, src/rootfinding.jl:530-549: in-step outputs first; the step that lands
          * on tmax stores its end point and leaves the loop BEFORE the event test of that step                  */
@@ -563,6 +578,7 @@ __device__ __forceinline__ bool tb_traj_step(TbTraj &T, double *__restrict__ smt
         }
     } else
         tb_store_psol(T, TB_JETS_ARGS, a);
+#endif
 #if TB_VARIANT == 1
     const bool f_now = tb_eval_event(smt, T.par, T.t0);
     const double g_now = TB_EV_G(eo);
@@ -605,7 +621,9 @@ __device__ __forceinline__ bool tb_traj_step(TbTraj &T, double *__restrict__ smt
     T.t0 = A_(T.t0, dt);
     tb_update_cache(smt, T.x0);
     T.nsteps += 1;
+#if !TB_FINAL_ONLY
     tb_store_step(T, smt, a);
+#endif
     if (T.nsteps > a.maxsteps) { T.st |= TB_ST_MAXSTEPS; return true; }
     if (!tb_isfinite_state(T.x0)) { T.st |= TB_ST_NONFINITE; return true; }
     return !(M_(T.sign, T.t0) < M_(T.sign, T.tmax));

@@ -352,6 +352,10 @@ static int integrate_host(tb_kernel *k, int64_t N, const double *q0, const doubl
     Loaded *l = nullptr;
     int rc = ensure_loaded(k, &l);
     if (rc) return rc;
+    if ((k->co.flags & TB_CF_FINAL_ONLY) && (k->co.kind == TB_KIND_PLAIN || k->co.kind == TB_KIND_EVENTS) && (trange || out->tv || out->xv || out->psol)) {
+        set_error("this kernel was built with TB_CF_FINAL_ONLY: no trange, per-step or dense output");
+        return TB_ERR_ARG;
+    }
     const bool lyapcol = k->co.kind == TB_KIND_LYAPCOL;
     if (lyapcol && (trange != nullptr) != ((k->co.flags & TB_CF_LYAP_TRANGE) != 0)) {
         set_error("TB_KIND_LYAPCOL: kernels built with TB_CF_LYAP_TRANGE serve tb_integrate_trange, the others tb_integrate");

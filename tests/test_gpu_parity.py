@@ -233,3 +233,20 @@ def test_fast_mode_is_close_to_parity_mode():
     rel = np.max(np.abs(a.xfinal - b.xfinal)) / np.max(np.abs(a.xfinal))
     assert rel < 1e-9, rel  # not bit-faithful: two roundings of the same recurrences drift apart (hard part 2)
     assert np.max(np.abs(a.nsteps - b.nsteps)) <= 1
+
+
+def test_final_only_build_matches_full_outputs_build():
+    """output='final' selects the TB_CF_FINAL_ONLY build of the plain kernel; it must return the bits of the build that
+    also carries the per-step / dense / trange code, and the C-ABI must refuse per-step outputs on it."""
+    q0, mu, _ = P.kepler_ensemble(300)
+    tm = 2 * np.pi * 2
+    for mode in ("parity", "fast"):
+        a = tb.taylorinteg(P.kepler_tape(), q0, 0.0, tm, 28, 1e-20, mu, maxsteps=2000, mode=mode)
+        b = tb.taylorinteg(P.kepler_tape(), q0, 0.0, tm, 28, 1e-20, mu, maxsteps=2000, mode=mode,
+                           kernel_opts={"full_outputs": True})
+        c = tb.taylorinteg(P.kepler_tape(), q0, 0.0, tm, 28, 1e-20, mu, maxsteps=2000, mode=mode, output="steps")
+        assert np.array_equal(a.xfinal, b.xfinal) and np.array_equal(a.nsteps, b.nsteps)
+        assert np.array_equal(a.xfinal, c.xfinal) and np.array_equal(a.tfinal, c.tfinal)
+    with pytest.raises(L.TaylorB200Error):
+        tb.taylorinteg(P.kepler_tape(), q0, 0.0, tm, 28, 1e-20, mu, maxsteps=50, output="steps",
+                       kernel_opts={"flags": 262144})

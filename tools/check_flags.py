@@ -10,7 +10,7 @@ flags = int(sys.argv[1]); rb = int(sys.argv[2]) if len(sys.argv) > 2 else 0
 q0, mu, _ = P.kepler_ensemble(3000)
 tm = 2 * np.pi * 3
 for mode in ("parity", "fast"):
-    a = tb.taylorinteg(P.kepler_tape(), q0, 0.0, tm, 28, 1e-20, mu, maxsteps=3000, mode=mode)
+    a = tb.taylorinteg(P.kepler_tape(), q0, 0.0, tm, 28, 1e-20, mu, maxsteps=3000, mode=mode, kernel_opts={"full_outputs": True})
     b = tb.taylorinteg(P.kepler_tape(), q0, 0.0, tm, 28, 1e-20, mu, maxsteps=3000, mode=mode, kernel_opts={"flags": flags, "reg_budget": rb})
     same = np.array_equal(a.xfinal, b.xfinal) and np.array_equal(a.nsteps, b.nsteps)
     rel = float(np.max(np.abs(a.xfinal - b.xfinal) / np.abs(a.xfinal).max(0)))
