@@ -182,7 +182,7 @@ typedef struct tb_compile_opts {
     int32_t reg_budget;    /* variant 2: doubles of jet storage kept in registers per trajectory (0 = default: 3 series, <0 = none) */
     int32_t min_blocks_per_sm; /* 0 = default                                 */
     int32_t flags;         /* TB_CF_*                                         */
-    int32_t reserved;
+    int32_t tmem_budget;   /* with TB_CF_TMEM: doubles of jet storage in tensor memory per trajectory (0 = as many as fit) */
 } tb_compile_opts_t;
 #define TB_CF_NO_DISK_CACHE 1 /* do not read/write the on-disk cubin cache    */
 #define TB_CF_KEEP_SOURCE 2   /* (always on) keep generated source for tb_get_source */
@@ -202,6 +202,10 @@ typedef struct tb_compile_opts {
 #define TB_CF_PAIR_POW 65536     /* parity: evaluate the two step-size powers in one interleaved body (measured slower) */
 #define TB_CF_LYAP_TRANGE 131072  /* TB_KIND_LYAPCOL: build the trange variant (tb_integrate_trange needs it) */
 #define TB_CF_FINAL_ONLY 262144   /* TB_KIND_PLAIN: final-state outputs only (no trange, tv/xv, psol) */
+#define TB_CF_TMEM 524288        /* TB_KIND_PLAIN: tensor memory as a third storage tier for recurrence-read series (tcgen05.ld/st) */
+#define TB_CF_TOPTRIM(t) (((t) & 15) << 20) /* register series: their top t coefficients live in shared memory */
+#define TB_CF_PREFETCH(d) (((d) & 15) << 24) /* storage loads are emitted 2*d source lines before their first use */
+#define TB_CF_MULAHEAD(d) (((d) & 7) << 28)  /* parity: the product of a sum term is emitted 2*d lines before its add (software pipelining) */
 #define TB_CF_SYNC_EVERY4 2048   /* with TB_CF_BLOCK_LOCKSTEP: barrier every 4th order only */
 
 /* ---- integration options: keyword arguments of taylorinteg -------------- */

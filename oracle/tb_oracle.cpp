@@ -266,6 +266,11 @@ int run_segment(Work &w, int first, int count, int kmax) {
     return 0;
 }
 
+/* Julia's min / max PROPAGATE NaN (Base.min(x::Float64, y::Float64)), unlike std::min / fmin: a NaN coefficient makes
+ * h NaN, then dt, the state and t0 NaN, and the driver loop ends on `sign*t0 < sign*tmax` being false (stepsize.jl:74, 86). */
+inline double jl_min(double a, double b) { return (a != a || b != b) ? std::numeric_limits<double>::quiet_NaN() : std::min(a, b); }
+inline double jl_max(double a, double b) { return (a != a || b != b) ? std::numeric_limits<double>::quiet_NaN() : std::max(a, b); }
+
 /* _stepsize: src/integrator/stepsize.jl:107-111 */
 inline double stepsize_k(const Math &m, double aux1, double epsilon, int k) {
     double aux = epsilon / aux1;
@@ -282,7 +287,7 @@ double stepsize1(const Math &m, const double *x, int P, double abseps, double re
         double aux1;
         if (abseps >= releps * x0norm) aux1 = stepsize_k(m, aux, abseps, k);
         else aux1 = stepsize_k(m, aux, releps * x0norm, k);
-        h = std::min(h, aux1);
+        h = jl_min(h, aux1);
     }
     return h;
 }
@@ -295,17 +300,17 @@ double second_stepsize(const Math &m, const double *x, int P) {
     for (int k = 1; k <= P - 2; k++) {
         double aux = std::fabs(x[k]);
         if (aux == 0.0) continue;
-        h = std::max(h, stepsize_k(m, aux, 1.0, k));
+        h = jl_max(h, stepsize_k(m, aux, 1.0, k));
     }
     return h;
 }
 /* stepsize(q::AbstractArray{Taylor1}, abs, rel): stepsize.jl:79-99 */
 double stepsize_vec(Work &w, int ncomp, double abseps, double releps) {
     double h = std::numeric_limits<double>::infinity();
-    for (int i = 0; i < ncomp; i++) h = std::min(h, stepsize1(w.math, w.X(i), w.P, abseps, releps));
+    for (int i = 0; i < ncomp; i++) h = jl_min(h, stepsize1(w.math, w.X(i), w.P, abseps, releps));
     if (std::isinf(h)) {
         h = 0.0;
-        for (int i = 0; i < ncomp; i++) h = std::max(h, second_stepsize(w.math, w.X(i), w.P));
+        for (int i = 0; i < ncomp; i++) h = jl_max(h, second_stepsize(w.math, w.X(i), w.P));
     }
     return h;
 }
@@ -360,7 +365,7 @@ int integ_plain(Work &w, const double *q0, double t0, double tmax, const tb_opts
         int rc = taylorstep(w, o, &dt);
         if (rc) return rc;
         if (dt == 0.0) { st |= TB_ST_ZERO_STEP; break; }
-        dt = sign_tstep * std::min(dt, sign_tstep * (tmax - t0));
+        dt = sign_tstep * jl_min(dt, sign_tstep * (tmax - t0));
         for (int i = 0; i < dof; i++) x0[i] = horner(w.X(i), P, dt);
         if (so && so->psol)
             for (int i = 0; i < dof; i++)
@@ -401,7 +406,7 @@ int integ_trange(Work &w, const double *q0, const double *trange, int64_t nt, co
         int rc = taylorstep(w, o, &dt);
         if (rc) return rc;
         if (dt == 0.0) { st |= TB_ST_ZERO_STEP; break; }
-        dt = sign_tstep * std::min(dt, sign_tstep * (tmax - t0));
+        dt = sign_tstep * jl_min(dt, sign_tstep * (tmax - t0));
         for (int i = 0; i < dof; i++) x0[i] = horner(w.X(i), P, dt);
         double tnext = t0 + dt;
         while (sign_tstep * t1 < sign_tstep * tnext) {
@@ -493,7 +498,7 @@ int integ_events(Work &w, const double *q0, double t0, double tmax, const tb_opt
         dt_old = dt;
         rc = taylorstep(w, o, &dt);
         if (rc) return rc;
-        dt = sign_tstep * std::min(dt, sign_tstep * (tmax - t0));
+        dt = sign_tstep * jl_min(dt, sign_tstep * (tmax - t0));
         for (int i = 0; i < dof; i++) x0[i] = horner(w.X(i), P, dt);
         if (trange) {
             const double tnext = t0 + dt;
@@ -670,7 +675,7 @@ int integ_lyap(Work &w, const double *q0, double t0, double tmax, const tb_opts_
         }
         double dt = stepsize_vec(w, dof, o.abstol, o.reltol);
         dt = clamp_(dt, o.minstepsize, o.maxstepsize);
-        dt = sign_tstep * std::min(dt, sign_tstep * (tmax - t0));
+        dt = sign_tstep * jl_min(dt, sign_tstep * (tmax - t0));
         for (int i = 0; i < nx; i++) x0[i] = horner(w.X(i), P, dt);
         for (int i = 0; i < dof * dof; i++) jt[i] = x0[dof + i];
         modifiedGS(jt.data(), QH.data(), RH.data(), dof);

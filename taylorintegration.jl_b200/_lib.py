@@ -64,7 +64,7 @@ class TbOdeDesc(C.Structure):
 class TbCompileOpts(C.Structure):
     _fields_ = [("order", C.c_int32), ("mode", C.c_int32), ("kind", C.c_int32), ("block_threads", C.c_int32),
                 ("reg_budget", C.c_int32), ("min_blocks_per_sm", C.c_int32), ("flags", C.c_int32),
-                ("reserved", C.c_int32)]
+                ("tmem_budget", C.c_int32)]
 
 
 class TbOpts(C.Structure):

@@ -36,7 +36,8 @@ class Kernel:
     """A compiled ensemble kernel (one per ODE x order x mode x kind)."""
 
     def __init__(self, tape: Tape, order: int, kind: int = L.KIND_PLAIN, mode: int = L.MODE_PARITY,
-                 block_threads: int = 0, flags: int = 0, reg_budget: int = 0, min_blocks_per_sm: int = 0):
+                 block_threads: int = 0, flags: int = 0, reg_budget: int = 0, min_blocks_per_sm: int = 0,
+                 tmem_budget: int = 0):
         lib = L.lib()
         self.tape, self.order, self.kind, self.mode = tape, int(order), kind, mode
         desc, keep = tape.c_desc()
@@ -46,7 +47,7 @@ class Kernel:
         co = L.TbCompileOpts()
         lib.tb_compile_opts_default(C.byref(co))
         co.order, co.mode, co.kind, co.block_threads = self.order, mode, kind, block_threads
-        co.flags, co.reg_budget, co.min_blocks_per_sm = flags, reg_budget, min_blocks_per_sm
+        co.flags, co.reg_budget, co.min_blocks_per_sm, co.tmem_budget = flags, reg_budget, min_blocks_per_sm, tmem_budget
         self._k = lib.tb_compile(self._ode, C.byref(co))
         del keep
         if not self._k:

@@ -66,7 +66,7 @@ std::string fmt(const char *f, ...) {
 bool u_is_num(int32_t o) { int k = TB_OPERAND_KIND(o); return k == TB_K_PAR || k == TB_K_IMM; }
 bool u_is_series(int32_t o) { int k = TB_OPERAND_KIND(o); return k == TB_K_X || k == TB_K_DX || k == TB_K_TMP || k == TB_K_TIME; }
 
-enum Place { PL_NONE = 0, PL_REG = 1, PL_SMEM = 2, PL_DERIVED = 3 };
+enum Place { PL_NONE = 0, PL_REG = 1, PL_SMEM = 2, PL_DERIVED = 3, PL_TMEM = 4 };
 
 struct SeriesInfo {
     int place = PL_NONE;
@@ -77,6 +77,7 @@ struct SeriesInfo {
     int trim = 0;     /* shared memory: coefficients 0..trim-1 are not stored (exactly recoverable, see analyse) */
     int32_t dx = 0;   /* trimmed state jet: its derivative series */
     int kreg = 0;     /* PL_REG: coefficients 0..kreg-1 live in registers, kreg..len-1 in shared memory (split series) */
+    int tbase = 0;    /* PL_TMEM: coefficient k lives in columns 2*(tbase + k), 2*(tbase + k) + 1 of the thread's window */
 };
 
 struct UGen {
@@ -87,7 +88,8 @@ struct UGen {
     const bool fast;
     std::map<int32_t, SeriesInfo> ser;
     std::string err;
-    int nreg = 0, nsm = 0;
+    int nreg = 0, nsm = 0, ntm = 0;
+    int tmem_doubles = 0; /* tensor-memory doubles per trajectory */
     int tmpc = 0;
 
     UGen(const Ode &o, const tb_compile_opts_t &c, Layout &l) : ode(o), co(c), L(l), P(c.order), fast(c.mode == TB_MODE_FAST) {}
@@ -99,9 +101,10 @@ struct UGen {
     }
     bool derive_x = true;
     bool split = false;   /* registers hold the LOW coefficients of every recurrence-read series (see analyse) */
+    int top_trim = 0;     /* register series keep coefficients 0..len-1-top_trim in registers, the rest in shared memory */
     bool trim_x = false;  /* parity: do not store x[0], x[1], x[2] of state jets that only Horner / stepsize read */
     int smem_doubles = 0; /* shared-memory doubles per trajectory */
-    void analyse(int reg_budget) {
+    void analyse(int reg_budget, int tmem_budget) {
         const tb_ode_desc_t &d = ode.desc;
         const double w = 0.5 * P * P;
         for (int j = 0; j < d.nops; j++) {
@@ -136,13 +139,30 @@ struct UGen {
         for (auto &kv : ser)
             if (kv.second.place != PL_DERIVED) order.push_back({-kv.second.reads, kv.first});
         std::sort(order.begin(), order.end());
-        int used = 0;
+        /* Tensor memory as a third storage tier (B200: 256 KB per SM, idle in a kernel without tcgen05.mma): a series
+         * that only the recurrences inside the jet body read (a temporary or a dx jet, not a state jet: Horner, the
+         * step size and the output code never touch it) may live in the thread's private TMEM window, written with
+         * tcgen05.st and read with tcgen05.ld (32x32b.x2: lane = thread, two 32-bit columns per double).  That frees
+         * shared memory (more resident trajectories) or registers (room for ptxas to hoist loads over the 8-cycle
+         * dependent FP64 chains).  The jet body must then run warp-converged (.sync.aligned), see tb_device_drv.cuh. */
+        std::set<int32_t> no_tmem;
+        for (int c = 0; c < d.dof; c++)
+            if (ser[TB_OPERAND(TB_K_X, c)].place == PL_DERIVED) no_tmem.insert(TB_OPERAND(TB_K_DX, c));
+        int used = 0, tused = 0;
         for (auto &pr : order) {
             SeriesInfo &si = ser[pr.second];
             si.len = P + 1;
-            if (si.reads > 0 && used + si.len <= reg_budget) { si.place = PL_REG; si.id = nreg++; used += si.len; si.kreg = si.len; }
-            else { si.place = PL_SMEM; si.id = nsm++; }
+            const bool state = TB_OPERAND_KIND(pr.second) == TB_K_X;
+            if (si.reads > 0 && used + si.len <= reg_budget) {
+                /* top_trim: the highest coefficients of a register series are read by a handful of terms per step
+                 * (coefficient j only at orders >= j); keeping them in shared memory costs a few loads and hands the
+                 * registers to ptxas, whose schedule of the dependent DMUL -> DADD chains is register-starved */
+                si.place = PL_REG; si.id = nreg++; used += si.len; si.kreg = std::max(1, si.len - top_trim);
+            } else if (si.reads > 0 && !state && !no_tmem.count(pr.second) && tused + si.len <= tmem_budget) {
+                si.place = PL_TMEM; si.id = ntm++; si.tbase = tused; tused += si.len;
+            } else { si.place = PL_SMEM; si.id = nsm++; }
         }
+        tmem_doubles = tused;
         if (split) {
             /* Split placement.  Coefficient j of a series read by recurrences is read P - j times per step, so the
              * top coefficients are cold: the register budget is spread over the LOW coefficients of ALL such series
@@ -167,7 +187,7 @@ struct UGen {
             for (int c = 0; c < d.dof; c++) {
                 int32_t x = TB_OPERAND(TB_K_X, c), dx = TB_OPERAND(TB_K_DX, c);
                 SeriesInfo &si = ser[x];
-                if (si.place != PL_SMEM || si.reads > 0 || !ser.count(dx) || ser[dx].place == PL_NONE || ser[dx].place == PL_DERIVED) continue;
+                if (si.place != PL_SMEM || si.reads > 0 || !ser.count(dx) || ser[dx].place == PL_NONE || ser[dx].place == PL_DERIVED || ser[dx].place == PL_TMEM) continue;
                 if (ser[dx].reads <= 0) continue;
                 si.trim = 3;
                 si.dx = dx;
@@ -210,6 +230,7 @@ struct UGen {
     std::map<Key, std::string> loaded;
     std::map<std::pair<std::string, std::string>, std::string> scaled;
     int cur = 0;
+    bool tm_dirty = false;
 
     static std::string vname(int32_t o, int k) {
         int kind = TB_OPERAND_KIND(o), i = TB_OPERAND_INDEX(o);
@@ -233,7 +254,12 @@ struct UGen {
         if (lt != loaded.end()) return lt->second;
         std::string n = fmt("l%d", tmpc++);
         if (r.idx < it->second.trim) { err = "internal: trimmed coefficient read by a recurrence"; return "0.0"; }
-        e.line("  const double %s = %s;", n.c_str(), sref(it->second, r.idx).c_str());
+        if (it->second.place == PL_TMEM) {
+            /* tcgen05.wait::st before the first tensor-memory load that follows a tensor-memory store */
+            if (tm_dirty) { e.line("  TB_TM_FENCE();"); tm_dirty = false; }
+            e.line("  const double %s = TB_TM_LD(%d);", n.c_str(), 2 * (it->second.tbase + r.idx));
+        }
+        else e.line("  const double %s = %s;", n.c_str(), sref(it->second, r.idx).c_str());
         loaded[Key(r.o, r.idx)] = n;
         return n;
     }
@@ -474,7 +500,14 @@ struct UGen {
         const char *a = c.acc.c_str();
         if (!fast) {
             if (i == 0) e.line("  double %s = M_(%s%s%s, %s);", a, c.neg ? "N_(" : "", x.c_str(), c.neg ? ")" : "", y.c_str());
-            else e.line("  %s = %s(%s, M_(%s, %s));", a, c.neg ? "B_" : "A_", a, x.c_str(), y.c_str());
+            else if (mulahead > 0) {
+                /* product and add on separate lines: hoist_lines() moves the product `mulahead` lines up so that the
+                 * DADD finds it finished (ptxas keeps the source order and would otherwise issue DMUL t; DADD acc, t
+                 * back to back through one temporary: 8 cycles of dependent-issue latency per term)             */
+                std::string pn = fmt("p%d", tmpc++);
+                e.line("  const double %s = M_(%s, %s);", pn.c_str(), x.c_str(), y.c_str());
+                e.line("  %s = %s(%s, %s);", a, c.neg ? "B_" : "A_", a, pn.c_str());
+            } else e.line("  %s = %s(%s, M_(%s, %s));", a, c.neg ? "B_" : "A_", a, x.c_str(), y.c_str());
         } else {
             const int j = (int)(i % (size_t)c.nacc);
             if (i < (size_t)c.nacc) e.line("  double %s_%d = %s * %s;", a, j, x.c_str(), y.c_str());
@@ -578,8 +611,75 @@ struct UGen {
         n.fin = true;
     }
 
+    /* Software prefetch.  A storage load is emitted where its first use is, and ptxas keeps a volatile load where the
+     * source has it: the consumer then eats the whole LDS latency (~30 cycles against ~8 cycles of FP64 issue per
+     * term with two warps per scheduler; ncu: the DMUL after each LDS holds 2/3 of the samples of such a chain).
+     * Every load of a group reads a coefficient stored by an EARLIER group (val() loads only indices below `cur`), so
+     * it may move up to the start of the group: each load line moves `prefetch` lines up, order among loads kept.  */
+    int prefetch = 0;  /* lines a storage load moves up (TB_CF_PREFETCH) */
+    int mulahead = 0;  /* lines a product moves up (TB_CF_MULAHEAD) */
+    static bool ident_char(char ch) { return (ch >= 'a' && ch <= 'z') || (ch >= 'A' && ch <= 'Z') || (ch >= '0' && ch <= '9') || ch == '_'; }
+    void hoist_lines(Em &e, size_t from) {
+        if ((prefetch <= 0 && mulahead <= 0) || from >= e.s.size()) return;
+        std::vector<std::string> lines;
+        size_t p = from;
+        while (p < e.s.size()) {
+            size_t q = e.s.find('\n', p);
+            if (q == std::string::npos) q = e.s.size();
+            lines.push_back(e.s.substr(p, q - p));
+            p = q + 1;
+        }
+        auto starts = [](const std::string &l, const char *pre) { return l.compare(0, strlen(pre), pre) == 0; };
+        auto is_load = [&](const std::string &l) {
+            return starts(l, "  const double l") && (l.find("= SB(") != std::string::npos || l.find("= TB_TM_LD(") != std::string::npos);
+        };
+        auto is_prod = [&](const std::string &l) { return starts(l, "  const double p") || starts(l, "  const double w"); };
+        /* name defined by a line ("  [const] double NAME = ...", "  double A, B; ..." is left alone) */
+        auto defined = [&](const std::string &l) -> std::string {
+            size_t d = l.find("double ");
+            if (d == std::string::npos || d > 8) return std::string();
+            size_t b = d + 7, q = b;
+            while (q < l.size() && ident_char(l[q])) q++;
+            return l.substr(b, q - b);
+        };
+        std::vector<std::string> out;
+        std::map<std::string, size_t> defpos; /* name -> index in `out` (kept current across insertions) */
+        size_t load_floor = 0;
+        auto insert_at = [&](size_t pos, const std::string &l) {
+            for (auto &kv : defpos) if (kv.second >= pos) kv.second++;
+            out.insert(out.begin() + (long)pos, l);
+            std::string nm = defined(l);
+            if (!nm.empty()) defpos[nm] = pos;
+        };
+        for (const std::string &l : lines) {
+            const bool ld = prefetch > 0 && is_load(l), pr = mulahead > 0 && is_prod(l);
+            if (l.find("TB_TM_FENCE") != std::string::npos) { insert_at(out.size(), l); load_floor = out.size(); continue; }
+            if (!ld && !pr) { insert_at(out.size(), l); continue; }
+            const size_t dist = (size_t)(ld ? prefetch : mulahead);
+            size_t pos = out.size() > dist ? out.size() - dist : 0;
+            if (ld) pos = std::max(pos, load_floor);
+            else { /* after the definition of everything the product reads */
+                const size_t eq = l.find('=');
+                size_t i = eq == std::string::npos ? 0 : eq + 1;
+                while (i < l.size()) {
+                    if (!ident_char(l[i]) || (l[i] >= '0' && l[i] <= '9')) { i++; continue; }
+                    size_t j = i;
+                    while (j < l.size() && ident_char(l[j])) j++;
+                    auto it = defpos.find(l.substr(i, j - i));
+                    if (it != defpos.end()) pos = std::max(pos, it->second + 1);
+                    i = j;
+                }
+            }
+            insert_at(pos, l);
+            if (ld) load_floor = pos + 1;
+        }
+        e.s.resize(from);
+        for (const std::string &l : out) { e.s += l; e.s += "\n"; }
+    }
+
     /* emit a group of sum nodes, chains interleaved one term per sweep */
     void emit_group(Em &e, std::vector<SNode> &g) {
+        const size_t group_start = e.s.size();
         loaded.clear();
         scaled.clear();
         size_t nchains = 0;
@@ -603,6 +703,7 @@ struct UGen {
             }
         }
         for (SNode &n : g) if (!n.fin && err.empty()) err = "internal: recurrence group did not complete";
+        hoist_lines(e, group_start);
     }
     /* parity-mode x / n for a small integer constant n: exact multiply for powers of two,
      * Markstein correction (tb_div_y) otherwise -- same bits as the IEEE division      */
@@ -616,6 +717,7 @@ struct UGen {
         if (it == ser.end()) return;
         if (it->second.place == PL_REG && k < it->second.kreg) e.line("  J.r%d[%d] = %s;", it->second.id, k, v.c_str());
         else if (it->second.place == PL_REG) e.line("  %s = %s;", sref(it->second, k).c_str(), v.c_str());
+        else if (it->second.place == PL_TMEM) { e.line("  TB_TM_ST(%d, %s);", 2 * (it->second.tbase + k), v.c_str()); tm_dirty = true; }
         else if (it->second.place == PL_SMEM && k >= it->second.trim) e.line("  %s = %s;", sref(it->second, k).c_str(), v.c_str());
     }
 
@@ -633,6 +735,7 @@ struct UGen {
         Em body;
         {
         Em &e = body;
+        tm_dirty = false; /* a step only loads coefficients it has stored itself: its first tensor-memory load follows a store */
         for (int c = 0; c < d.dof; c++) {
             e.line("  const double vX%d_0 = x0[%d];", c, c);
             define(e, TB_OPERAND(TB_K_X, c), 0, fmt("vX%d_0", c));
@@ -698,7 +801,7 @@ struct UGen {
             if (!any) { err = "tape has a dependency cycle or an undefined operand (dx not defined?)"; break; }
         }
         }
-        const char *sig = "(TbJets &J, double *__restrict__ smt, const double *__restrict__ par, const double t0, const double *__restrict__ x0)";
+        const char *sig = "(TbJets &J, double *__restrict__ smt, const unsigned tm, const double *__restrict__ par, const double t0, const double *__restrict__ x0)";
         const bool quick = !fast && !(co.flags & 64);
         if (quick) {
             /* parity mode, two copies of the body: the QUICK one divides with unguarded Markstein /
@@ -726,7 +829,10 @@ struct UGen {
         out.line("}");
         if (quick) {
             out.line("__device__ __forceinline__ void tb_u_jets%s {", sig);
-            out.line("  if (tb_u_jets_q(J, smt, par, t0, x0) >= TB_RNG_SPAN) tb_u_jets_s(J, smt, par, t0, x0);");
+            /* tensor-memory accesses are warp-collective: when any lane needs the guarded divisions the whole warp
+             * takes the safe copy (same bits either way)                                                          */
+            if (ntm > 0) out.line("  if (__any_sync(0xffffffffu, tb_u_jets_q(J, smt, tm, par, t0, x0) >= TB_RNG_SPAN)) tb_u_jets_s(J, smt, tm, par, t0, x0);");
+            else out.line("  if (tb_u_jets_q(J, smt, tm, par, t0, x0) >= TB_RNG_SPAN) tb_u_jets_s(J, smt, tm, par, t0, x0);");
             out.line("}");
         }
     }
@@ -799,7 +905,21 @@ int generate_unrolled(const Ode &ode, const tb_compile_opts_t &co, Layout &L, st
     g.derive_x = parity ? (co.flags & 512) != 0 : !(co.flags & 256);
     g.trim_x = parity && co.kind == TB_KIND_PLAIN && !(co.flags & 4096);
     g.split = (co.flags & 8192) != 0;
-    g.analyse(budget);
+    g.top_trim = (co.flags >> 20) & 15; /* TB_CF_TOPTRIM(t) */
+    g.prefetch = (co.flags >> 24) & 15; /* TB_CF_PREFETCH(d) */
+    g.mulahead = parity ? (co.flags >> 28) & 7 : 0; /* TB_CF_MULAHEAD(d), lines = 2*d */
+    g.mulahead *= 2; g.prefetch *= 2;
+    /* tensor memory: 512 columns x 128 lanes of 32 bits per SM; warp w reaches lanes 32*(w%4)..+31, so the warps that
+     * share a lane quadrant split the columns: 256 threads -> 256 columns = 128 doubles per thread.  TB_CF_TMEM
+     * turns the tier on (plain kernels; the jet body of the event / team kernels runs in divergent code).        */
+    int tmem_budget = 0;
+    if ((co.flags & TB_CF_TMEM) && co.kind == TB_KIND_PLAIN) {
+        const int btmax = co.block_threads > 0 ? co.block_threads : 256;
+        const int share = ((btmax + 31) / 32 + 3) / 4;
+        tmem_budget = (512 / share) / 2;
+        if (co.tmem_budget > 0) tmem_budget = std::min(tmem_budget, co.tmem_budget);
+    }
+    g.analyse(budget, tmem_budget);
     L.variant = 2;
     L.nx = d.dof;
     L.nslot = g.nsm;
@@ -845,9 +965,15 @@ int generate_unrolled(const Ode &ode, const tb_compile_opts_t &co, Layout &L, st
      * the plain Kepler kernel gains nothing from it (+-1 %), so it stays opt-in there (TB_CF_STEP_LOCKSTEP)   */
     const bool step_lock = (co.flags & 1024) || (co.kind == TB_KIND_EVENTS && !(co.flags & 16384));
     e.line("#define TB_BAR %d", (co.flags & 128) ? 1 : step_lock ? 2 : 0);
+    e.line("#define TB_TMEM %d", g.ntm > 0 ? 1 : 0);
+    if (g.ntm > 0) {
+        const int share = (bt / 32 + 3) / 4;
+        if (2 * g.tmem_doubles > 512 / share) { err = "internal: tensor-memory window overflow"; return TB_ERR_ARG; }
+        e.line("#define TB_TM_COLS %d /* columns of the per-warp window (%d warps share a lane quadrant) */", (512 / share) & ~1, share);
+    }
     e.s += embedded_math_h();
     e.s += embedded_device_pre();
-    e.line("/* placement: %d series in registers, %d in shared memory */", g.nreg, g.nsm);
+    e.line("/* placement: %d series in registers, %d in shared memory, %d in tensor memory */", g.nreg, g.nsm, g.ntm);
     e.line("struct TbJets {");
     for (int i = 0; i < g.nreg; i++) {
         int kr = np1;

@@ -72,7 +72,7 @@ __device__ __forceinline__ double tb_stepsize1(const double *__restrict__ smt, i
         double rel = M_(releps, x0norm);
         double eps = (abseps >= rel) ? abseps : rel;
         double h1 = tb_stepsize_k(aux, eps, k);
-        h = fmin(h, h1);
+        h = tb_jmin(h, h1);
     }
     return h;
 }
@@ -87,7 +87,7 @@ __device__ __noinline__ double tb_second_stepsize(const double *__restrict__ smt
     for (int k = 1; k <= TB_P - 2; k++) {
         double aux = fabs(S(slot, k));
         if (aux == 0.0) continue;
-        h = fmax(h, tb_stepsize_k(aux, 1.0, k));
+        h = tb_jmax(h, tb_stepsize_k(aux, 1.0, k));
     }
     return h;
 }
@@ -98,10 +98,10 @@ __device__ __noinline__ double tb_second_stepsize(const double *__restrict__ smt
 __device__ __forceinline__ double tb_stepsize(const double *__restrict__ smt, const TbArgs &a) {
     double h = TB_INF;
 #pragma unroll
-    for (int i = 0; i < TB_DOF; i++) h = fmin(h, tb_stepsize1(smt, i, a.abstol, a.reltol));
+    for (int i = 0; i < TB_DOF; i++) h = tb_jmin(h, tb_stepsize1(smt, i, a.abstol, a.reltol));
     if (h == TB_INF) {
         h = 0.0;
-        for (int i = 0; i < TB_DOF; i++) h = fmax(h, tb_second_stepsize(smt, i));
+        for (int i = 0; i < TB_DOF; i++) h = tb_jmax(h, tb_second_stepsize(smt, i));
     }
     /* clamp(h, lo, hi) */
     h = (h < a.minstep) ? a.minstep : ((h > a.maxstep) ? a.maxstep : h);
@@ -142,7 +142,7 @@ __device__ __noinline__ double tb_second_stepsize_arr(const double *x) {
     for (int k = 1; k <= TB_P - 2; k++) {
         double aux = fabs(x[k]);
         if (aux == 0.0) continue;
-        h = fmax(h, tb_stepsize_k(aux, 1.0, k));
+        h = tb_jmax(h, tb_stepsize_k(aux, 1.0, k));
     }
     return h;
 }
@@ -174,7 +174,9 @@ __device__ __forceinline__ double tb_u_stepsize(const TbJets &J, const double *_
          * differ by more than 2^-40 relative cannot swap order after the 1/k-th power).  Only
          * components within 2^-40 of the maximum are evaluated as well: same bits as the
          * reference's loop over all components (stepsize.jl:83-86), 2 pow calls instead of 2*dof.
-         * NaN coefficients drop out of fmax here exactly as they drop out of min there.       */
+         * Julia's min PROPAGATES NaN: one NaN |x_c[k]| makes h NaN (then dt, the state and t0, and the
+         * driver loop ends); fmax drops NaNs, so they are tracked separately (`anynan`).          */
+        bool anynan = false;
 #if TB_STEPSIZE_PAIR
         /* TB_CF_PAIR_POW: the two powers in ONE straight-line body (tb_pow_pair, same bits) so that their dependent
          * chains overlap; measured slower than two calls on both benchmark kernels, kept as an option            */
@@ -194,7 +196,7 @@ __device__ __forceinline__ double tb_u_stepsize(const TbJets &J, const double *_
         for (int k = TB_P - 1; k <= TB_P; k++) {
             double m = 0.0, ac[TB_NQ];
 #pragma unroll
-            for (int c = 0; c < TB_NQ; c++) { ac[c] = fabs(TB_X(c, k)); m = fmax(m, ac[c]); }
+            for (int c = 0; c < TB_NQ; c++) { ac[c] = fabs(TB_X(c, k)); m = fmax(m, ac[c]); anynan = anynan || (ac[c] != ac[c]); }
             if (m != 0.0) {
 #if TB_STEPSIZE_PAIR
                 double hk = both ? (k == TB_P ? hp.b : hp.a) : tb_stepsize_k(m, a.abstol, k);
@@ -208,6 +210,7 @@ __device__ __forceinline__ double tb_u_stepsize(const TbJets &J, const double *_
                 h = fmin(h, hk);
             }
         }
+        if (anynan) h = TB_NAN;
     } else
 #endif
     {
@@ -220,7 +223,7 @@ __device__ __forceinline__ double tb_u_stepsize(const TbJets &J, const double *_
                 if (aux == 0.0) continue;
                 const double rel = M_(a.reltol, x0norm);
                 const double eps = (a.abstol >= rel) ? a.abstol : rel;
-                h = fmin(h, tb_stepsize_k(aux, eps, k));
+                h = tb_jmin(h, tb_stepsize_k(aux, eps, k));
             }
         }
     }
@@ -231,7 +234,7 @@ __device__ __forceinline__ double tb_u_stepsize(const TbJets &J, const double *_
         for (int c = 0; c < TB_NQ; c++) {
 #pragma unroll
             for (int k = 0; k <= TB_P; k++) buf[k] = TB_X(c, k);
-            h = fmax(h, tb_second_stepsize_arr(buf));
+            h = tb_jmax(h, tb_second_stepsize_arr(buf));
         }
     }
     h = (h < a.minstep) ? a.minstep : ((h > a.maxstep) ? a.maxstep : h);
@@ -420,7 +423,7 @@ __device__ __forceinline__ bool tb_traj_init(TbTraj &T, double *__restrict__ smt
     } else { /* variant 2: g is a state component (generated accessors), jets in registers / shared memory */
         TbJets J;
         const double *x0 = T.x0;
-        tb_u_jets(J, smt, T.par, T.t0, x0);
+        tb_u_jets(J, smt, 0u, T.par, T.t0, x0);
         T.f_old = TB_EV_GATE_EXPR;
         T.g_old = tb_u_gcoef(J, smt, x0, a.eventorder);
     }
@@ -448,7 +451,7 @@ __device__ __forceinline__ bool tb_traj_init(TbTraj &T, double *__restrict__ smt
 #define TB_JETS_DECL TbJets J; const double *x0 = T.x0;
 #define TB_JETS_ARGS J, smt, x0
 #define TB_JETS_PARAMS const TbJets &J, const double *__restrict__ smt, const double *__restrict__ x0
-#define TB_COMPUTE_JETS(T) tb_u_jets(J, smt, (T).par, (T).t0, x0)
+#define TB_COMPUTE_JETS(T) tb_u_jets(J, smt, tb_tm, (T).par, (T).t0, x0)
 #define TB_STEPSIZE(a) tb_u_stepsize(J, smt, x0, (a))
 #define TB_HORNER(c, dt) tb_u_horner(J, smt, x0, (c), (dt))
 #define TB_XCOEF(c, k) TB_X((c), (k))
@@ -480,7 +483,7 @@ __device__ __forceinline__ void tb_store_psol(const TbTraj &T, TB_JETS_PARAMS, c
 }
 
 /* One iteration of the driver loop; returns true when the trajectory is done. */
-__device__ __forceinline__ bool tb_traj_step(TbTraj &T, double *__restrict__ smt, const TbArgs &a, const bool live) {
+__device__ __forceinline__ bool tb_traj_step(TbTraj &T, double *__restrict__ smt, const unsigned tb_tm, const TbArgs &a, const bool live) {
 #if TB_KIND == 0
     /* taylorinteg!: src/integrator/taylorinteg.jl:356-378 (t0,tmax) and 607-639 (trange) */
     TB_JETS_DECL
@@ -489,7 +492,7 @@ __device__ __forceinline__ bool tb_traj_step(TbTraj &T, double *__restrict__ smt
     double dt = TB_STEPSIZE(a);
     if (dt == 0.0) { T.st |= TB_ST_ZERO_STEP; return true; }
     const double rem = B_(T.tmax, T.t0);
-    dt = M_(T.sign, fmin(dt, M_(T.sign, rem)));
+    dt = M_(T.sign, TB_DTMIN(dt, M_(T.sign, rem)));
     double xn[TB_DOF];
 #pragma unroll
     for (int c = 0; c < TB_DOF; c++) xn[c] = TB_HORNER(c, dt);
@@ -547,7 +550,7 @@ __device__ __forceinline__ bool tb_traj_step(TbTraj &T, double *__restrict__ smt
     T.dt_old = T.dt;
     TB_COMPUTE_JETS(T);
     double dt = TB_STEPSIZE(a);
-    dt = M_(T.sign, fmin(dt, M_(T.sign, B_(T.tmax, T.t0))));
+    dt = M_(T.sign, TB_DTMIN(dt, M_(T.sign, B_(T.tmax, T.t0))));
     T.dt = dt;
     double xn[TB_DOF];
 #pragma unroll
@@ -640,7 +643,7 @@ __device__ __forceinline__ bool tb_traj_step(TbTraj &T, double *__restrict__ smt
 #pragma unroll 1
     for (int k = 1; k < TB_P; k++) tb_var_k(smt, T.par, k);
     double dt = tb_stepsize(smt, a);
-    dt = M_(T.sign, fmin(dt, M_(T.sign, B_(T.tmax, T.t0))));
+    dt = M_(T.sign, TB_DTMIN(dt, M_(T.sign, B_(T.tmax, T.t0))));
 #pragma unroll
     for (int c = 0; c < TB_NX; c++) T.x0[c] = tb_horner(smt, c, dt);
     double QH[TB_DOF * TB_DOF], Rd[TB_DOF];
@@ -700,8 +703,14 @@ extern "C" __global__ void __launch_bounds__(TB_BT, TB_MINB) tb_ensemble_kernel(
     double *__restrict__ smt = tb_sm + threadIdx.x;
     const unsigned full = 0xffffffffu;
     const int lane = threadIdx.x & 31;
+#if TB_TMEM
+    __shared__ unsigned tb_tm_slot;
+    const unsigned tb_tm = tb_tm_alloc(&tb_tm_slot);
+#else
+    const unsigned tb_tm = 0u;
+#endif
     TbTraj T;
-#if TB_BAR
+#if TB_BAR || TB_TMEM
     /* idle lanes execute the jet code on whatever T holds: give it defined numbers */
 #pragma unroll
     for (int c = 0; c < TB_NX; c++) T.x0[c] = 1.0;
@@ -740,17 +749,26 @@ extern "C" __global__ void __launch_bounds__(TB_BT, TB_MINB) tb_ensemble_kernel(
 #if TB_BAR == 2
         /* step lockstep: one barrier per step only; the warps start every step together and drift by
          * less than the instruction cache holds, so a line fetched by the leader serves the others */
-        if (have) { if (tb_traj_step(T, smt, a, true)) { tb_traj_finish(T, a); have = false; } }
+        if (have) { if (tb_traj_step(T, smt, tb_tm, a, true)) { tb_traj_finish(T, a); have = false; } }
 #else
-        if (tb_traj_step(T, smt, a, have)) { tb_traj_finish(T, a); have = false; }
+        if (tb_traj_step(T, smt, tb_tm, a, have)) { tb_traj_finish(T, a); have = false; }
 #endif
 #else
         if (!__any_sync(full, have)) { if (!(a.lockstep && more)) break; else continue; }
+#if TB_TMEM
+        /* the jet body holds warp-collective tensor-memory accesses: every lane of the warp runs it (the vote above
+         * reconverged the warp), idle lanes on stale numbers whose results are dropped                             */
+        if (tb_traj_step(T, smt, tb_tm, a, have)) { tb_traj_finish(T, a); have = false; }
+#else
         if (have) {
-            if (tb_traj_step(T, smt, a, true)) { tb_traj_finish(T, a); have = false; }
+            if (tb_traj_step(T, smt, tb_tm, a, true)) { tb_traj_finish(T, a); have = false; }
         }
 #endif
+#endif
     }
+#if TB_TMEM
+    tb_tm_free(&tb_tm_slot);
+#endif
 }
 
 #else /* TB_KIND == 3 */
@@ -824,11 +842,11 @@ __device__ __forceinline__ double tb_pick_col(const double *M, int r, int col) {
     return v;
 }
 
-__device__ __forceinline__ bool tb_traj_step(TbTraj &T, double *__restrict__ smt, const TbArgs &a, const bool live) {
+__device__ __forceinline__ bool tb_traj_step(TbTraj &T, double *__restrict__ smt, const unsigned tb_tm, const TbArgs &a, const bool live) {
     TB_JETS_DECL
     TB_COMPUTE_JETS(T);
     double dt = TB_STEPSIZE(a); /* over the TB_NQ components of x only (lyapunovspectrum.jl:262) */
-    dt = M_(T.sign, fmin(dt, M_(T.sign, B_(T.tmax, T.t0))));
+    dt = M_(T.sign, TB_DTMIN(dt, M_(T.sign, B_(T.tmax, T.t0))));
     double xn[TB_NX];
     TB_UNROLL_V2
     for (int c = 0; c < TB_NX; c++) xn[c] = TB_HORNER(c, dt);
@@ -926,6 +944,7 @@ extern "C" __global__ void __launch_bounds__(TB_BT, TB_MINB) tb_ensemble_kernel(
     const unsigned full = 0xffffffffu;
     const int lane = threadIdx.x & 31;
     const bool member = lane < TB_TPW * TB_TEAM;
+    const unsigned tb_tm = 0u; /* no tensor-memory tier in the team kernel */
     TbTraj T;
     T.lit = lane % TB_TEAM;
     T.leader = lane - T.lit;
@@ -946,7 +965,7 @@ extern "C" __global__ void __launch_bounds__(TB_BT, TB_MINB) tb_ensemble_kernel(
         if (!__any_sync(full, have)) break;
 #endif
         if (have) {
-            if (tb_traj_step(T, smt, a, true)) { tb_traj_finish(T, a); have = false; }
+            if (tb_traj_step(T, smt, tb_tm, a, true)) { tb_traj_finish(T, a); have = false; }
         }
     }
 }
@@ -958,7 +977,16 @@ extern "C" __global__ void __launch_bounds__(TB_BT, TB_MINB) tb_ensemble_kernel(
 extern "C" __global__ void __launch_bounds__(TB_BT, TB_MINB) tb_jet_kernel(const TbArgs a) {
     extern __shared__ double tb_sm[];
     double *__restrict__ smt = tb_sm + threadIdx.x;
-    for (long long i = (long long)blockIdx.x * TB_BT + threadIdx.x; i < a.N; i += (long long)gridDim.x * TB_BT) {
+#if TB_TMEM
+    __shared__ unsigned tb_tm_slot;
+    const unsigned tb_tm = tb_tm_alloc(&tb_tm_slot);
+#else
+    const unsigned tb_tm = 0u;
+#endif
+    /* whole warps iterate (the jet body may hold warp-collective accesses); lanes past N recompute trajectory N-1 */
+    for (long long i0 = (long long)blockIdx.x * TB_BT + (threadIdx.x & ~31); i0 < a.N; i0 += (long long)gridDim.x * TB_BT) {
+        const bool live = i0 + (threadIdx.x & 31) < a.N;
+        const long long i = live ? i0 + (threadIdx.x & 31) : a.N - 1;
         double par[TB_NPAR > 0 ? TB_NPAR : 1];
         for (int j = 0; j < TB_NPAR; j++) par[j] = a.params_per_traj ? a.params[(long long)j * a.N + i] : a.params[j];
         struct { double x0[TB_DOF]; double par[TB_NPAR > 0 ? TB_NPAR : 1]; double t0; } T;
@@ -970,8 +998,8 @@ extern "C" __global__ void __launch_bounds__(TB_BT, TB_MINB) tb_jet_kernel(const
         TB_JETS_DECL
         TB_COMPUTE_JETS(T);
         double dt = TB_STEPSIZE(a);
-        if (a.dtout) a.dtout[i] = dt;
-        if (a.xjet) {
+        if (a.dtout && live) a.dtout[i] = dt;
+        if (a.xjet && live) {
             TB_UNROLL_V2
             for (int c = 0; c < TB_DOF; c++) {
                 TB_UNROLL_V2
@@ -979,6 +1007,9 @@ extern "C" __global__ void __launch_bounds__(TB_BT, TB_MINB) tb_jet_kernel(const
             }
         }
     }
+#if TB_TMEM
+    tb_tm_free(&tb_tm_slot);
+#endif
 }
 
 #else

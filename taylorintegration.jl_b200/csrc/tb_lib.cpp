@@ -139,6 +139,7 @@ struct tb_kernel {
     std::vector<char> cubin;
     int regs = -1, local_bytes = -1;
     std::mutex mu;
+    std::mutex call_mu; /* serialises the host-buffer entry points on this handle (they share the arena) */
     std::map<int, tb::Loaded> loaded; /* per device */
     /* grow-only device arena for the host-buffer entry points, per device */
     std::map<int, std::pair<char *, size_t>> arena;
@@ -198,16 +199,18 @@ static int validate(const tb_ode_desc_t &d, std::string &why) {
     return 1;
 }
 
-/* parse "Used N registers" / "bytes stack frame" of the ptxas -v log for the ensemble kernel */
+/* parse "Used N registers" / "N bytes stack frame" of the ptxas -v log for the ensemble kernel.  The stack-frame
+ * line reads "    360 bytes stack frame, 192 bytes spill stores, ..." (the number precedes the words). */
 static void parse_ptxas(const std::string &log, int *regs, int *local_bytes) {
     size_t p = log.find("tb_ensemble_kernel");
     if (p == std::string::npos) return;
     size_t q = log.find("Used ", p);
     if (q != std::string::npos) *regs = atoi(log.c_str() + q + 5);
-    size_t s = log.find("bytes stack frame", p);
-    if (s != std::string::npos) {
-        size_t b = log.rfind('\n', s);
-        *local_bytes = atoi(log.c_str() + (b == std::string::npos ? 0 : b + 1));
+    size_t s = log.find(" bytes stack frame", p);
+    if (s != std::string::npos && (q == std::string::npos || s < q + 400)) {
+        size_t b = s;
+        while (b > 0 && log[b - 1] >= '0' && log[b - 1] <= '9') b--;
+        *local_bytes = atoi(log.c_str() + b);
     }
 }
 
@@ -340,64 +343,109 @@ static int arena_get(tb_kernel *k, size_t bytes, Arena &A) {
     return TB_OK;
 }
 
-static int integrate_host(tb_kernel *k, int64_t N, const double *q0, const double *params, double t0, double tmax,
-                          const double *trange, int64_t nt, const tb_opts_t *opts, tb_out_t *out) {
-    if (!k || !opts || !out || N < 0 || !q0) { set_error("tb_integrate: bad argument"); return TB_ERR_ARG; }
-    if (trange && nt < 2) { set_error("tb_integrate_trange: trange needs at least two points"); return TB_ERR_ARG; }
+/* Argument / build-flag checks shared by the host-buffer and the device-buffer entry points. */
+static int check_call(const char *fn, tb_kernel *k, int64_t N, const void *q0, const void *params, const double *trange,
+                      int64_t nt, const tb_opts_t *opts, const tb_out_t *out) {
+    const std::string f = fn;
+    if (!k || !opts || !out || N < 0) { set_error(f + ": bad argument"); return TB_ERR_ARG; }
+    if (N > 0 && !q0) { set_error(f + ": q0 is NULL"); return TB_ERR_ARG; }
+    if (trange && nt < 2) { set_error(f + ": trange needs at least two points"); return TB_ERR_ARG; }
     if (trange && k->co.kind == TB_KIND_LYAP) { set_error("trange is implemented for TB_KIND_PLAIN, TB_KIND_EVENTS and TB_KIND_LYAPCOL kernels"); return TB_ERR_UNSUPPORTED; }
     const tb_ode_desc_t &d = k->ode.desc;
-    if (d.npar > 0 && !params) { set_error("tb_integrate: params is NULL"); return TB_ERR_ARG; }
-    if (k->co.kind == TB_KIND_EVENTS && opts->eventorder > k->co.order) { set_error("order must be >= eventorder (rootfinding.jl:321)"); return TB_ERR_ARG; }
-    if (N == 0) return TB_OK;
-    Loaded *l = nullptr;
-    int rc = ensure_loaded(k, &l);
-    if (rc) return rc;
-    if ((k->co.flags & TB_CF_FINAL_ONLY) && (k->co.kind == TB_KIND_PLAIN || k->co.kind == TB_KIND_EVENTS) && (trange || out->tv || out->xv || out->psol)) {
+    if (N > 0 && d.npar > 0 && !params) { set_error(f + ": params is NULL"); return TB_ERR_ARG; }
+    if (opts->maxsteps < 0 || opts->event_capacity < 0 || opts->steps_stride < 0) { set_error(f + ": negative maxsteps / event_capacity / steps_stride"); return TB_ERR_ARG; }
+    if (k->co.kind == TB_KIND_EVENTS && (opts->eventorder < 0 || opts->eventorder > k->co.order)) { set_error("order must be >= eventorder >= 0 (rootfinding.jl:321)"); return TB_ERR_ARG; }
+    if ((k->co.flags & TB_CF_FINAL_ONLY) && (k->co.kind == TB_KIND_PLAIN || k->co.kind == TB_KIND_EVENTS) && (trange || out->tv || out->xv || out->psol || out->xv_trange)) {
         set_error("this kernel was built with TB_CF_FINAL_ONLY: no trange, per-step or dense output");
         return TB_ERR_ARG;
     }
     const bool lyapcol = k->co.kind == TB_KIND_LYAPCOL;
     if (lyapcol && (trange != nullptr) != ((k->co.flags & TB_CF_LYAP_TRANGE) != 0)) {
-        set_error("TB_KIND_LYAPCOL: kernels built with TB_CF_LYAP_TRANGE serve tb_integrate_trange, the others tb_integrate");
+        set_error("TB_KIND_LYAPCOL: kernels built with TB_CF_LYAP_TRANGE serve trange calls, the others (t0, tmax) calls");
         return TB_ERR_ARG;
     }
-    const size_t dof = lyapcol ? d.dof / 2 : d.dof, n = (size_t)N, np1 = k->co.order + 1;
     if (lyapcol && out->psol) { set_error("TB_KIND_LYAPCOL has no dense output"); return TB_ERR_UNSUPPORTED; }
+    const int64_t stride = opts->steps_stride ? opts->steps_stride : opts->maxsteps + 1;
+    if (!trange && (out->tv || out->xv || out->psol || out->lambda_v) && stride < opts->maxsteps + 1) {
+        set_error(f + ": steps_stride must be >= maxsteps + 1");
+        return TB_ERR_ARG;
+    }
+    return TB_OK;
+}
+
+struct EventPair { /* RAII: destroyed on every exit path */
+    cudaEvent_t e0 = nullptr, e1 = nullptr;
+    ~EventPair() { if (e0) cudaEventDestroy(e0); if (e1) cudaEventDestroy(e1); }
+};
+struct OwnStream {
+    cudaStream_t s = nullptr;
+    ~OwnStream() { if (s) cudaStreamDestroy(s); }
+};
+
+static int integrate_host(tb_kernel *k, int64_t N, const double *q0, const double *params, double t0, double tmax,
+                          const double *trange, int64_t nt, const tb_opts_t *opts, tb_out_t *out) {
+    int rc = check_call("tb_integrate", k, N, q0, params, trange, nt, opts, out);
+    if (rc) return rc;
+    const tb_ode_desc_t &d = k->ode.desc;
+    if (N == 0) return TB_OK;
+    Loaded *l = nullptr;
+    rc = ensure_loaded(k, &l);
+    if (rc) return rc;
+    const bool lyapcol = k->co.kind == TB_KIND_LYAPCOL;
+    const size_t dof = lyapcol ? d.dof / 2 : d.dof, n = (size_t)N, np1 = k->co.order + 1;
     const size_t stride = opts->steps_stride ? opts->steps_stride : opts->maxsteps + 1;
     const size_t cap = opts->event_capacity > 0 ? opts->event_capacity : (size_t)(opts->maxsteps + 1);
     const size_t npar_elems = d.npar ? (opts->params_per_traj ? (size_t)d.npar * n : (size_t)d.npar) : 0;
-    struct Item { void **dptr; void *host; size_t bytes; };
+    /* rows: the buffer is [.. x rows x N] and only the first `used` rows (known after the kernel: max nsteps + 1,
+     * max nevents) are copied back; planes = leading extent (dof, dof*(order+1)), 1 = a plain copy of everything */
+    enum { ROWS_ALL = 0, ROWS_STEPS = 1, ROWS_STEPS_M1 = 2, ROWS_EVENTS = 3 };
+    struct Item { void **dptr; void *host; size_t bytes; int rows_kind; size_t planes, rows; };
     tb_out_t dv;
     memset(&dv, 0, sizeof dv);
     std::vector<Item> outs;
-    auto want = [&](void *host, void **dptr, size_t bytes) { if (host) outs.push_back({dptr, host, bytes}); };
+    auto want = [&](void *host, void **dptr, size_t bytes, int rk = ROWS_ALL, size_t planes = 1, size_t rows = 0) {
+        if (host) outs.push_back({dptr, host, bytes, rk, planes, rows});
+    };
+    const bool events = k->co.kind == TB_KIND_EVENTS;
+    std::vector<int64_t> ns_tmp;
+    std::vector<int32_t> ne_tmp;
     want(out->xfinal, (void **)&dv.xfinal, dof * n * 8);
     want(out->tfinal, (void **)&dv.tfinal, n * 8);
-    want(out->nsteps, (void **)&dv.nsteps, n * 8);
+    const bool per_step = !trange && (out->tv || out->xv || out->psol || out->lambda_v);
+    int64_t *h_ns = out->nsteps;
+    if (!h_ns && per_step) { ns_tmp.resize(n); h_ns = ns_tmp.data(); }
+    want(h_ns, (void **)&dv.nsteps, n * 8);
     want(out->status, (void **)&dv.status, n * 4);
     if (trange) want(out->xv_trange, (void **)&dv.xv_trange, dof * (size_t)nt * n * 8);
     else {
-        want(out->tv, (void **)&dv.tv, stride * n * 8);
-        want(out->xv, (void **)&dv.xv, dof * stride * n * 8);
-        want(out->psol, (void **)&dv.psol, dof * np1 * stride * n * 8);
+        want(out->tv, (void **)&dv.tv, stride * n * 8, ROWS_STEPS, 1, stride);
+        want(out->xv, (void **)&dv.xv, dof * stride * n * 8, ROWS_STEPS, dof, stride);
+        want(out->psol, (void **)&dv.psol, dof * np1 * stride * n * 8, ROWS_STEPS_M1, dof * np1, stride);
     }
-    if (k->co.kind == TB_KIND_EVENTS) {
-        want(out->tevents, (void **)&dv.tevents, cap * n * 8);
-        want(out->xevents, (void **)&dv.xevents, dof * cap * n * 8);
-        want(out->gresids, (void **)&dv.gresids, cap * n * 8);
-        want(out->nevents, (void **)&dv.nevents, n * 4);
+    int32_t *h_ne = out->nevents;
+    if (events) {
+        const bool any_ev = out->tevents || out->xevents || out->gresids;
+        if (!h_ne && any_ev) { ne_tmp.resize(n); h_ne = ne_tmp.data(); }
+        want(out->tevents, (void **)&dv.tevents, cap * n * 8, ROWS_EVENTS, 1, cap);
+        want(out->xevents, (void **)&dv.xevents, dof * cap * n * 8, ROWS_EVENTS, dof, cap);
+        want(out->gresids, (void **)&dv.gresids, cap * n * 8, ROWS_EVENTS, 1, cap);
+        want(h_ne, (void **)&dv.nevents, n * 4);
     }
     if (k->co.kind == TB_KIND_LYAP || lyapcol) {
         want(out->lambda, (void **)&dv.lambda, dof * n * 8);
-        if (!trange) want(out->lambda_v, (void **)&dv.lambda_v, dof * stride * n * 8);
+        if (!trange) want(out->lambda_v, (void **)&dv.lambda_v, dof * stride * n * 8, ROWS_STEPS, dof, stride);
         else want(out->lambda_v, (void **)&dv.lambda_v, dof * (size_t)nt * n * 8); /* exponents at trange, [dof x nt x N] */
     }
     size_t total = rup(256) + rup(dof * n * 8) + rup(npar_elems * 8) + rup((size_t)(trange ? nt : 0) * 8);
     for (auto &it : outs) total += rup(it.bytes);
+    /* one host-buffer call at a time per kernel handle: the arena and the work counter belong to the call */
+    std::lock_guard<std::mutex> call_lock(k->call_mu);
     Arena A;
     rc = arena_get(k, total, A);
     if (rc) return rc;
-    cudaStream_t st = 0;
+    OwnStream os;
+    TB_CUDA(cudaStreamCreateWithFlags(&os.s, cudaStreamNonBlocking));
+    cudaStream_t st = os.s;
     void *work = A.take<char>(256);
     double *d_q0 = A.take<double>(dof * n);
     double *d_par = npar_elems ? A.take<double>(npar_elems) : nullptr;
@@ -407,27 +455,46 @@ static int integrate_host(tb_kernel *k, int64_t N, const double *q0, const doubl
     TB_CUDA(cudaMemcpyAsync(d_q0, q0, dof * n * 8, cudaMemcpyHostToDevice, st));
     if (d_par) TB_CUDA(cudaMemcpyAsync(d_par, params, npar_elems * 8, cudaMemcpyHostToDevice, st));
     if (d_tr) TB_CUDA(cudaMemcpyAsync(d_tr, trange, (size_t)nt * 8, cudaMemcpyHostToDevice, st));
-    /* buffers the kernel fills only partially start from zero */
+    /* buffers the kernel fills only partially start from zero (a device memset runs at HBM speed; the expensive part,
+     * the copy back over PCIe, is limited to the rows in use below) */
     for (auto &it : outs)
-        if (it.host == out->tv || it.host == out->xv || it.host == out->psol || it.host == out->tevents ||
-            it.host == out->xevents || it.host == out->gresids || it.host == out->lambda_v)
-            TB_CUDA(cudaMemsetAsync(*it.dptr, 0, it.bytes, st));
+        if (it.rows_kind != ROWS_ALL) TB_CUDA(cudaMemsetAsync(*it.dptr, 0, it.bytes, st));
     TbArgs a;
     fill_args(a, N, d_q0, d_par, t0, tmax, d_tr, nt, *opts, dv, work);
-    cudaEvent_t e0, e1;
-    TB_CUDA(cudaEventCreate(&e0));
-    TB_CUDA(cudaEventCreate(&e1));
-    TB_CUDA(cudaEventRecord(e0, st));
+    EventPair ev;
+    TB_CUDA(cudaEventCreate(&ev.e0));
+    TB_CUDA(cudaEventCreate(&ev.e1));
+    TB_CUDA(cudaEventRecord(ev.e0, st));
     rc = launch(k, l, l->ensemble, a, true, st);
     if (rc) return rc;
-    TB_CUDA(cudaEventRecord(e1, st));
-    for (auto &it : outs) TB_CUDA(cudaMemcpyAsync(it.host, *it.dptr, it.bytes, cudaMemcpyDeviceToHost, st));
+    TB_CUDA(cudaEventRecord(ev.e1, st));
+    bool partial = false;
+    for (auto &it : outs) {
+        if (it.rows_kind != ROWS_ALL) { partial = true; continue; }
+        TB_CUDA(cudaMemcpyAsync(it.host, *it.dptr, it.bytes, cudaMemcpyDeviceToHost, st));
+    }
+    if (partial) {
+        /* the counters are on the host now: copy rows [0, used) of every [planes x rows x N] buffer.  Rows past
+         * `used` of the caller's buffers are left untouched (they are past every trajectory's nsteps / nevents). */
+        TB_CUDA(cudaStreamSynchronize(st));
+        int64_t max_ns = 0;
+        int32_t max_ne = 0;
+        if (h_ns && per_step) for (size_t i = 0; i < n; i++) max_ns = std::max(max_ns, h_ns[i]);
+        if (h_ne) for (size_t i = 0; i < n; i++) max_ne = std::max(max_ne, h_ne[i]);
+        for (auto &it : outs) {
+            if (it.rows_kind == ROWS_ALL) continue;
+            size_t used = it.rows_kind == ROWS_EVENTS ? (size_t)max_ne
+                        : it.rows_kind == ROWS_STEPS ? (size_t)max_ns + 1 : (size_t)max_ns;
+            used = std::min(used, it.rows);
+            if (used == 0) continue;
+            TB_CUDA(cudaMemcpy2DAsync(it.host, it.rows * n * 8, *it.dptr, it.rows * n * 8, used * n * 8, it.planes,
+                                      cudaMemcpyDeviceToHost, st));
+        }
+    }
     TB_CUDA(cudaStreamSynchronize(st));
     float ms = -1.f;
-    cudaEventElapsedTime(&ms, e0, e1);
+    cudaEventElapsedTime(&ms, ev.e0, ev.e1);
     set_last_kernel_ms(ms);
-    cudaEventDestroy(e0);
-    cudaEventDestroy(e1);
     return TB_OK;
 }
 
@@ -513,7 +580,8 @@ static std::string cache_path(const std::string &source, int mode) {
     mix(source.data(), source.size());
     /* the NVRTC version is NOT part of the key: a process that imported torch first resolves libnvrtc.so.12 to
      * torch's bundled 12.8, whose ptxas spills where 12.9 does not; cubins prebuilt by build() (CUDA 12.9) win */
-    const std::string tag = "|sm_100a|mode" + std::to_string(mode);
+    std::string tag = "|sm_100a|mode" + std::to_string(mode);
+    if (const char *x = getenv("TB_PTXAS_EXTRA")) tag += std::string("|") + x; /* experiment hook, see tb_compile */
     mix(tag.data(), tag.size());
     char name[64];
     snprintf(name, sizeof name, "/%016llx", h);
@@ -548,8 +616,19 @@ tb_kernel_t *tb_compile(const tb_ode_t *ode, const tb_compile_opts_t *co) {
     if (!cpath.empty() && read_file(cpath + ".cubin", k->cubin) && !k->cubin.empty()) {
         std::vector<char> lg;
         if (read_file(cpath + ".log", lg)) k->log.assign(lg.begin(), lg.end());
-        parse_ptxas(k->log, &k->regs, &k->local_bytes);
-        return k;
+        /* a cubin written by an OLDER NVRTC than the one running is stale (toolkit upgrade): recompile.  One written
+         * by a newer NVRTC is kept: that is build()'s CUDA 12.9 cubin met by a process whose libnvrtc.so.12 resolved
+         * to torch's bundled 12.8, whose ptxas spills where 12.9 does not.                                         */
+        int cmaj = 0, cmin = 0, rmaj = 0, rmin = 0;
+        const size_t vp = k->log.rfind("compiled by NVRTC ");
+        const bool stamped = vp != std::string::npos && sscanf(k->log.c_str() + vp, "compiled by NVRTC %d.%d", &cmaj, &cmin) == 2;
+        nvrtcVersion(&rmaj, &rmin);
+        if (stamped && (rmaj < cmaj || (rmaj == cmaj && rmin <= cmin))) {
+            parse_ptxas(k->log, &k->regs, &k->local_bytes);
+            return k;
+        }
+        k->cubin.clear();
+        k->log.clear();
     }
     nvrtcProgram prog;
     if (nvrtcCreateProgram(&prog, k->source.c_str(), "tb_kernel.cu", 0, nullptr, nullptr) != NVRTC_SUCCESS) {
@@ -562,6 +641,9 @@ tb_kernel_t *tb_compile(const tb_ode_t *ode, const tb_compile_opts_t *co) {
     o.push_back(k->co.mode == TB_MODE_PARITY ? "--fmad=false" : "--fmad=true");
     o.push_back("--prec-div=true");
     o.push_back("--prec-sqrt=true");
+    /* experiment hook: extra ptxas options (e.g. TB_PTXAS_EXTRA=-O2), part of the cache key */
+    std::string extra;
+    if (const char *x = getenv("TB_PTXAS_EXTRA")) { extra = std::string("--ptxas-options=") + x; o.push_back(extra.c_str()); }
     nvrtcResult r = nvrtcCompileProgram(prog, (int)o.size(), o.data());
     size_t ls = 0;
     nvrtcGetProgramLogSize(prog, &ls);
@@ -629,8 +711,9 @@ size_t tb_work_bytes(void) { return 256; }
 int tb_integrate_device(tb_kernel_t *k, int64_t N, const double *d_q0, const double *d_params, double t0, double tmax,
                         const double *d_trange, int64_t nt, const tb_opts_t *opts, const tb_out_t *d_out, void *d_work,
                         void *stream) {
-    if (!k || !opts || !d_out || !d_work || N < 0) { set_error("tb_integrate_device: bad argument"); return TB_ERR_ARG; }
-    if (d_trange && k->co.kind == TB_KIND_LYAP) { set_error("trange is implemented for TB_KIND_PLAIN, TB_KIND_EVENTS and TB_KIND_LYAPCOL kernels"); return TB_ERR_UNSUPPORTED; }
+    if (!d_work) { set_error("tb_integrate_device: d_work is NULL"); return TB_ERR_ARG; }
+    int rc0 = check_call("tb_integrate_device", k, N, d_q0, d_params, d_trange, nt, opts, d_out);
+    if (rc0) return rc0;
     if (N == 0) return TB_OK;
     Loaded *l = nullptr;
     int rc = ensure_loaded(k, &l);
@@ -656,6 +739,8 @@ int tb_jet(tb_kernel_t *k, int64_t N, const double *q0, const double *params, do
     const tb_ode_desc_t &d = k->ode.desc;
     const size_t dof = d.dof, n = (size_t)N, np1 = k->co.order + 1;
     const size_t npar_elems = d.npar ? (opts->params_per_traj ? (size_t)d.npar * n : (size_t)d.npar) : 0;
+    if (d.npar > 0 && !params) { set_error("tb_jet: params is NULL"); return TB_ERR_ARG; }
+    std::lock_guard<std::mutex> call_lock(k->call_mu);
     Arena A;
     rc = arena_get(k, rup(dof * n * 8) + rup(npar_elems * 8) + rup(dof * np1 * n * 8) + rup(n * 8) + 256, A);
     if (rc) return rc;

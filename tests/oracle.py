@@ -191,3 +191,58 @@ def integrate_tn(tape: tb.Tape, order: int, nvars: int, varorder: int, q0, t0=0.
     assert rc == 0, rc
     del keep
     return res
+
+
+# ---- generic (parse_eqs = false) path: oracle/libtb_generic.so ---------------------------------------------------
+_SO_GEN = os.path.join(_ROOT, "oracle", "libtb_generic.so")
+_lib_gen = None
+
+
+def lib_generic() -> C.CDLL:
+    global _lib_gen
+    if _lib_gen is None:
+        if not os.path.exists(_SO_GEN):
+            build()
+        o = C.CDLL(_SO_GEN)
+        vp = C.c_void_p
+        o.tbg_problem_name.restype = C.c_char_p
+        o.tbg_jet.argtypes = [C.c_int, C.c_int, vp, vp, C.c_double, vp]
+        o.tbg_integrate.argtypes = [C.c_int, C.c_int, vp, vp, C.c_double, C.c_double, C.POINTER(L.TbOpts), vp, vp, vp, vp,
+                                    vp, vp]
+        _lib_gen = o
+    return _lib_gen
+
+
+def generic_problem(name: str) -> int:
+    g = lib_generic()
+    names = [g.tbg_problem_name(i).decode() for i in range(g.tbg_problem_count())]
+    return names.index(name)
+
+
+def generic_jet(name: str, order: int, q0, params=None, t0=0.0) -> np.ndarray:
+    """jets [dof, order+1] from the reference's generic jetcoeffs! (src/integrator/jetcoeffs.jl:66-92)."""
+    pid = generic_problem(name)
+    q0 = np.ascontiguousarray(q0, dtype=np.float64)
+    par = np.ascontiguousarray(np.atleast_1d(params if params is not None else [0.0]), dtype=np.float64)
+    xj = np.zeros((q0.shape[0], order + 1))
+    rc = lib_generic().tbg_jet(pid, order, _p(q0), _p(par), float(t0), _p(xj))
+    assert rc == 0, rc
+    return xj
+
+
+def generic_integrate(name: str, order: int, q0, t0, tmax, params=None, **kw):
+    """One trajectory through taylorinteg with parse_eqs = false; returns (tv[n+1], xv[dof, n+1], status)."""
+    pid = generic_problem(name)
+    q0 = np.ascontiguousarray(q0, dtype=np.float64)
+    par = np.ascontiguousarray(np.atleast_1d(params if params is not None else [0.0]), dtype=np.float64)
+    o = _opts(**kw)
+    stride = o.maxsteps + 1
+    dof = q0.shape[0]
+    tv, xv = np.zeros(stride), np.zeros((dof, stride))
+    xf, tf = np.zeros(dof), np.zeros(1)
+    ns, st = np.zeros(1, dtype=np.int64), np.zeros(1, dtype=np.int32)
+    rc = lib_generic().tbg_integrate(pid, order, _p(q0), _p(par), float(t0), float(tmax), C.byref(o), _p(tv), _p(xv),
+                                     _p(xf), _p(tf), _p(ns), _p(st))
+    assert rc == 0, rc
+    n = int(ns[0])
+    return tv[: n + 1].copy(), xv[:, : n + 1].copy(), int(st[0])

@@ -23,6 +23,11 @@ scale = 1.0
 for a in sys.argv[1:]:
     if a.startswith("--scale"):
         scale = float(a.split("=")[1])
+kflags = 0
+for a in sys.argv[1:]:
+    if a.startswith("--kflags"):
+        kflags = int(a.split("=")[1])
+KOPTS = {"flags": kflags} if kflags else None
 which = args or ["pendulum", "lorenz", "manyspin", "jet2", "jet4"]
 mode = "fast" if "--fast" in sys.argv else "parity"
 peak_tf, _ = tb.fp64_peak(0.3)
@@ -58,7 +63,7 @@ if "pendulum" in which:  # config 2
     q0 = P.pendulum_ensemble(N)
     q0 = q0[0] if isinstance(q0, tuple) else q0
     sol, secs = timed(lambda: tb.taylorinteg_events(tape, q0, 0.0, 100.0, 25, 1e-20, maxsteps=2000, event_capacity=64,
-                                                    mode=mode, output="final"))
+                                                    mode=mode, output="final", kernel_opts=KOPTS))
     nev = int(sol.nevents.sum())
     report("2 pendulum+events", f"N={N}, order 25, abstol 1e-20, tmax 100, g = x[2], event capacity 64", sol.nsteps.sum(), secs,
            1685, (sol.status == 0).all(), {"events": nev})
@@ -70,7 +75,7 @@ if "lorenz" in which:  # config 3
     par = np.stack([np.full(N, 16.0), rho, np.full(N, 4.0)])
     q0 = np.tile(np.array([[19.0], [20.0], [50.0]]), (1, N))
     sol, secs = timed(lambda: tb.lyap_taylorinteg(tape, q0, 0.0, 100.0, 28, 1e-20, par, maxsteps=20000, mode=mode,
-                                                  output="final"))
+                                                  output="final", kernel_opts=KOPTS))
     report("3 lorenz lyapunov", f"N={N} rho in [28,92], sigma 16, beta 4, order 28, abstol 1e-20, tmax 100", sol.nsteps.sum(), secs,
            24700, (sol.status == 0).all(), {"sum_lambda_mean": float(sol.lam.sum(0).mean())})
 
