@@ -206,6 +206,7 @@ typedef struct tb_compile_opts {
 #define TB_CF_TOPTRIM(t) (((t) & 15) << 20) /* register series: their top t coefficients live in shared memory */
 #define TB_CF_PREFETCH(d) (((d) & 15) << 24) /* storage loads are emitted 2*d source lines before their first use */
 #define TB_CF_MULAHEAD(d) (((d) & 7) << 28)  /* parity: the product of a sum term is emitted 2*d lines before its add (software pipelining) */
+#define TB_CF_NO_SWPIPE 32768     /* parity: no software pipelining of loads / products (default: PREFETCH(8), MULAHEAD(4)) */
 #define TB_CF_SYNC_EVERY4 2048   /* with TB_CF_BLOCK_LOCKSTEP: barrier every 4th order only */
 
 /* ---- integration options: keyword arguments of taylorinteg -------------- */
@@ -289,6 +290,16 @@ int tb_integrate(tb_kernel_t *k, int64_t N, const double *q0, const double *para
  * holds the exponents at the output times, [dof x nt x N], out->lambda the ones at trange[nt-1]).                     */
 int tb_integrate_trange(tb_kernel_t *k, int64_t N, const double *q0, const double *params,
                         const double *trange, int64_t nt, const tb_opts_t *opts, tb_out_t *out);
+
+/* ONE ensemble over several GPUs of this process.  The N trajectories are cut into round-robin blocks
+ * of `block` (0 = 4096); device `devices[d]` takes blocks d, d + ndev, ...; one host thread per device runs the
+ * host-buffer path above on its shard and writes its results straight into the caller's [rows x N] buffers.
+ * trange == NULL: the (t0, tmax) drivers; otherwise tb_integrate_trange semantics (t0 / tmax ignored).  All outputs of
+ * tb_out_t are supported.  tb_last_kernel_ms() afterwards reports the slowest device's kernel.  The reference has no
+ * multi-device path; this stands for a `Threads.@threads` loop over taylorinteg calls (docs/src/root_finding.md:121-132). */
+int tb_integrate_multi(tb_kernel_t *k, const int32_t *devices, int32_t ndev, int64_t block, int64_t N,
+                       const double *q0, const double *params, double t0, double tmax, const double *trange,
+                       int64_t nt, const tb_opts_t *opts, tb_out_t *out);
 
 /* DEVICE buffers, asynchronous on `stream` (a cudaStream_t; NULL = default).
  * `work` is a device int64 scratch of tb_work_bytes() bytes.                 */

@@ -86,7 +86,7 @@ class TbOut(C.Structure):
 
 EXPORTS = [
     "tb_abi_version", "tb_last_error", "tb_ode_create", "tb_ode_free", "tb_opts_default", "tb_compile_opts_default",
-    "tb_generate_source", "tb_compile", "tb_kernel_free", "tb_kernel_source", "tb_kernel_log", "tb_kernel_info",
+    "tb_generate_source", "tb_compile", "tb_integrate_multi", "tb_kernel_free", "tb_kernel_source", "tb_kernel_log", "tb_kernel_info",
     "tb_kernel_cubin", "tb_integrate", "tb_integrate_trange", "tb_work_bytes", "tb_integrate_device",
     "tb_launch_count", "tb_jet", "tb_dense_eval", "tb_fp64_peak", "tb_device_count", "tb_set_device",
     "tb_tn_create", "tb_tn_free", "tb_tn_ncoef", "tb_tn_monomials", "tb_tn_integrate",
@@ -138,6 +138,8 @@ def lib() -> C.CDLL:
     L.tb_kernel_cubin.argtypes = [vp, C.POINTER(C.c_size_t)]
     L.tb_integrate.argtypes = [vp, C.c_int64, vp, vp, C.c_double, C.c_double, C.POINTER(TbOpts), C.POINTER(TbOut)]
     L.tb_integrate_trange.argtypes = [vp, C.c_int64, vp, vp, vp, C.c_int64, C.POINTER(TbOpts), C.POINTER(TbOut)]
+    L.tb_integrate_multi.argtypes = [vp, vp, C.c_int32, C.c_int64, C.c_int64, vp, vp, C.c_double, C.c_double, vp, C.c_int64,
+                                     C.POINTER(TbOpts), C.POINTER(TbOut)]
     L.tb_work_bytes.restype = C.c_size_t
     L.tb_integrate_device.argtypes = [vp, C.c_int64, vp, vp, C.c_double, C.c_double, vp, C.c_int64,
                                       C.POINTER(TbOpts), C.POINTER(TbOut), vp, vp]

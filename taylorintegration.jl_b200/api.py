@@ -301,7 +301,7 @@ def _warn_status(status: np.ndarray) -> None:
 
 def _integrate(tape: Tape, kind: int, q0, t0, tmax, trange, order, abstol, params, *, maxsteps, dense, reltol,
                minstepsize, maxstepsize, eventorder=0, newtoniter=10, nrabstol=_EPS, event_capacity=0, mode="parity",
-               output=None, kernel_opts=None):
+               output=None, kernel_opts=None, devices=None, block=4096):
     q0 = np.asarray(q0, dtype=np.float64)
     single = q0.ndim == 1
     q = np.ascontiguousarray(q0[:, None] if single else q0)
@@ -371,6 +371,10 @@ def _integrate(tape: Tape, kind: int, q0, t0, tmax, trange, order, abstol, param
         if wide:
             L.check(lib.tb_wide_integrate(k.handle, N, _ptr(q), _ptr(par), float(tr[0]), float(tr[-1]), _ptr(tr), tr.size,
                                           C.byref(o), C.byref(out)), "tb_wide_integrate")
+        elif devices is not None:
+            dv = np.ascontiguousarray(devices, dtype=np.int32)
+            L.check(lib.tb_integrate_multi(k.handle, _ptr(dv), dv.size, int(block), N, _ptr(q), _ptr(par), float(tr[0]),
+                                           float(tr[-1]), _ptr(tr), tr.size, C.byref(o), C.byref(out)), "tb_integrate_multi")
         else:
             L.check(lib.tb_integrate_trange(k.handle, N, _ptr(q), _ptr(par), _ptr(tr), tr.size, C.byref(o),
                                             C.byref(out)), "tb_integrate_trange")
@@ -396,8 +400,13 @@ def _integrate(tape: Tape, kind: int, q0, t0, tmax, trange, order, abstol, param
         if kind == L.KIND_LYAP:
             sol.lam = np.empty((dof, N))
             out.lambda_ = sol.lam.ctypes.data_as(L._DP)
-        L.check(lib.tb_integrate(k.handle, N, _ptr(q), _ptr(par), float(t0), float(tmax), C.byref(o), C.byref(out)),
-                "tb_integrate")
+        if devices is not None:  # one ensemble over several GPUs of this process (tb_integrate_multi)
+            dv = np.ascontiguousarray(devices, dtype=np.int32)
+            L.check(lib.tb_integrate_multi(k.handle, _ptr(dv), dv.size, int(block), N, _ptr(q), _ptr(par), float(t0),
+                                           float(tmax), None, 0, C.byref(o), C.byref(out)), "tb_integrate_multi")
+        else:
+            L.check(lib.tb_integrate(k.handle, N, _ptr(q), _ptr(par), float(t0), float(tmax), C.byref(o), C.byref(out)),
+                    "tb_integrate")
     _warn_status(status)
     if single:
         return sol.trajectory(0)
@@ -406,8 +415,10 @@ def _integrate(tape: Tape, kind: int, q0, t0, tmax, trange, order, abstol, param
 
 def taylorinteg(f, *args, maxsteps: int = 500, parse_eqs: bool = True, dense: bool = True, reltol: float = 0.0,
                 minstepsize: float = 0.0, maxstepsize: float = np.inf, eventorder: int = 0, newtoniter: int = 10,
-                nrabstol: float = _EPS, event_capacity: int = 0, mode="parity", output=None, kernel_opts=None):
-    """See the module docstring.  `parse_eqs` is accepted for signature compatibility: the tape path is the only
+                nrabstol: float = _EPS, event_capacity: int = 0, mode="parity", output=None, kernel_opts=None,
+                devices=None, block: int = 4096):
+    """See the module docstring.  `devices=[0, 1, ...]` shards ONE ensemble over several GPUs of this process in
+    round-robin blocks of `block` trajectories (tb_integrate_multi).  `parse_eqs` is accepted for signature compatibility: the tape path is the only
     path (there is no generic `jetcoeffs!` fallback on the GPU)."""
     g = None
     if len(args) >= 1 and (callable(args[0]) and not isinstance(args[0], (np.ndarray, Tape))):
@@ -426,7 +437,7 @@ def taylorinteg(f, *args, maxsteps: int = 500, parse_eqs: bool = True, dense: bo
     return _integrate(tape, kind, q0, t0, tmax, trange, int(order), abstol, params, maxsteps=maxsteps, dense=dense,
                       reltol=reltol, minstepsize=minstepsize, maxstepsize=maxstepsize, eventorder=eventorder,
                       newtoniter=newtoniter, nrabstol=nrabstol, event_capacity=event_capacity, mode=mode, output=output,
-                      kernel_opts=kernel_opts)
+                      kernel_opts=kernel_opts, devices=devices, block=block)
 
 
 def taylorinteg_events(tape: Tape, q0, t0, tmax, order, abstol, params=None, trange=None, **kw):
@@ -441,7 +452,8 @@ def taylorinteg_events(tape: Tape, q0, t0, tmax, order, abstol, params=None, tra
 
 
 def lyap_taylorinteg(f, q0, *args, maxsteps: int = 500, parse_eqs: bool = True, reltol: float = 0.0,
-                     minstepsize: float = 0.0, maxstepsize: float = np.inf, mode="parity", output=None, kernel_opts=None):
+                     minstepsize: float = 0.0, maxstepsize: float = np.inf, mode="parity", output=None, kernel_opts=None,
+                     devices=None, block: int = 4096):
     """Lyapunov spectrum (src/lyapunovspectrum.jl:293-429).  The Jacobian always comes from first-order forward
     mode on the tape (the reference's TaylorN path); `jacobianfunc` is accepted and ignored, since the reference
     requires both to agree (test/lyapunov.jl:294-296)."""
@@ -460,7 +472,7 @@ def lyap_taylorinteg(f, q0, *args, maxsteps: int = 500, parse_eqs: bool = True, 
         raise ValueError("the tape has no Jacobian; build it with taylorize(..., jacobian=True)")
     return _integrate(tape, L.KIND_LYAP, q0, t0, tmax, trange, int(order), abstol, params, maxsteps=maxsteps, dense=False,
                       reltol=reltol, minstepsize=minstepsize, maxstepsize=maxstepsize, mode=mode, output=output,
-                      kernel_opts=kernel_opts)
+                      kernel_opts=kernel_opts, devices=devices, block=block)
 
 
 def fp64_peak(seconds: float = 0.5) -> Tuple[float, float]:

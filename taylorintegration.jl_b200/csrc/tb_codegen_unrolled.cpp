@@ -908,6 +908,9 @@ int generate_unrolled(const Ode &ode, const tb_compile_opts_t &co, Layout &L, st
     g.top_trim = (co.flags >> 20) & 15; /* TB_CF_TOPTRIM(t) */
     g.prefetch = (co.flags >> 24) & 15; /* TB_CF_PREFETCH(d) */
     g.mulahead = parity ? (co.flags >> 28) & 7 : 0; /* TB_CF_MULAHEAD(d), lines = 2*d */
+    /* default of the parity plain / team kernels (B200 sweep, round 2: Kepler-28 +5 %, Lorenz column kernel +1.6 %,
+     * pendulum events +-0): loads 16 lines and products 8 lines ahead; deeper pipelines spill more than they hide */
+    if (parity && g.prefetch == 0 && g.mulahead == 0 && !(co.flags & TB_CF_NO_SWPIPE) && co.kind != TB_KIND_EVENTS) { g.prefetch = 8; g.mulahead = 4; }
     g.mulahead *= 2; g.prefetch *= 2;
     /* tensor memory: 512 columns x 128 lanes of 32 bits per SM; warp w reaches lanes 32*(w%4)..+31, so the warps that
      * share a lane quadrant split the columns: 256 threads -> 256 columns = 128 doubles per thread.  TB_CF_TMEM

@@ -25,6 +25,7 @@
 #include <cstring>
 #include <limits>
 #include <mutex>
+#include <thread>
 
 namespace tb {
 
@@ -139,7 +140,7 @@ struct tb_kernel {
     std::vector<char> cubin;
     int regs = -1, local_bytes = -1;
     std::mutex mu;
-    std::mutex call_mu; /* serialises the host-buffer entry points on this handle (they share the arena) */
+    std::map<int, std::mutex> call_mu; /* per device: serialises the host-buffer entry points (they share that device's arena) */
     std::map<int, tb::Loaded> loaded; /* per device */
     /* grow-only device arena for the host-buffer entry points, per device */
     std::map<int, std::pair<char *, size_t>> arena;
@@ -343,6 +344,14 @@ static int arena_get(tb_kernel *k, size_t bytes, Arena &A) {
     return TB_OK;
 }
 
+/* the mutex that serialises host-buffer calls on the CURRENT device for this kernel handle */
+static std::mutex &device_call_mutex(tb_kernel *k) {
+    int dev = 0;
+    cudaGetDevice(&dev);
+    std::lock_guard<std::mutex> lk(k->mu);
+    return k->call_mu[dev];
+}
+
 /* Argument / build-flag checks shared by the host-buffer and the device-buffer entry points. */
 static int check_call(const char *fn, tb_kernel *k, int64_t N, const void *q0, const void *params, const double *trange,
                       int64_t nt, const tb_opts_t *opts, const tb_out_t *out) {
@@ -439,7 +448,7 @@ static int integrate_host(tb_kernel *k, int64_t N, const double *q0, const doubl
     size_t total = rup(256) + rup(dof * n * 8) + rup(npar_elems * 8) + rup((size_t)(trange ? nt : 0) * 8);
     for (auto &it : outs) total += rup(it.bytes);
     /* one host-buffer call at a time per kernel handle: the arena and the work counter belong to the call */
-    std::lock_guard<std::mutex> call_lock(k->call_mu);
+    std::lock_guard<std::mutex> call_lock(device_call_mutex(k));
     Arena A;
     rc = arena_get(k, total, A);
     if (rc) return rc;
@@ -706,6 +715,127 @@ int tb_integrate_trange(tb_kernel_t *k, int64_t N, const double *q0, const doubl
     return integrate_host(k, N, q0, params, trange[0], trange[nt > 0 ? nt - 1 : 0], trange, nt, opts, out);
 }
 
+/* ---- one ensemble over several GPUs of one process -------------------------------------------------------------
+ * trajectories are independent, so the ensemble is cut into round-robin blocks of `block`
+ * trajectories (cost-ordered ensembles: contiguous halves would hand one GPU all the expensive orbits), device d
+ * takes blocks d, d + ndev, ...; one host thread per device packs its shard, runs the ordinary host-buffer path on
+ * that device (own stream, own arena) and scatters the results straight into the caller's [rows x N] buffers.
+ * No collective is needed inside one process.                                                                   */
+} /* extern "C" */
+
+struct ShardCopy {
+    int64_t N, block;
+    int dev_index, ndev;
+    int64_t count() const {
+        int64_t n = 0;
+        for (int64_t b = dev_index; b * block < N; b += ndev) n += std::min(block, N - b * block);
+        return n;
+    }
+    /* global [rows x N] -> local [rows x n] */
+    template <class T> void pack(const T *g, T *l, size_t rows, int64_t n) const {
+        for (size_t r = 0; r < rows; r++) {
+            int64_t o = 0;
+            for (int64_t b = dev_index; b * block < N; b += ndev) {
+                const int64_t len = std::min(block, N - b * block);
+                memcpy(l + r * (size_t)n + o, g + r * (size_t)N + b * block, (size_t)len * sizeof(T));
+                o += len;
+            }
+        }
+    }
+    template <class T> void unpack(T *g, const T *l, size_t rows, int64_t n) const {
+        for (size_t r = 0; r < rows; r++) {
+            int64_t o = 0;
+            for (int64_t b = dev_index; b * block < N; b += ndev) {
+                const int64_t len = std::min(block, N - b * block);
+                memcpy(g + r * (size_t)N + b * block, l + r * (size_t)n + o, (size_t)len * sizeof(T));
+                o += len;
+            }
+        }
+    }
+};
+
+extern "C" {
+
+int tb_integrate_multi(tb_kernel_t *k, const int32_t *devices, int32_t ndev, int64_t block, int64_t N, const double *q0,
+                       const double *params, double t0, double tmax, const double *trange, int64_t nt,
+                       const tb_opts_t *opts, tb_out_t *out) {
+    if (!devices || ndev < 1) { set_error("tb_integrate_multi: no devices"); return TB_ERR_ARG; }
+    if (block <= 0) block = 4096;
+    int rc = check_call("tb_integrate_multi", k, N, q0, params, trange, nt, opts, out);
+    if (rc) return rc;
+    if (trange) { t0 = trange[0]; tmax = trange[nt - 1]; }
+    if (N == 0) return TB_OK;
+    const tb_ode_desc_t &d = k->ode.desc;
+    const bool lyapcol = k->co.kind == TB_KIND_LYAPCOL;
+    const size_t dof = lyapcol ? d.dof / 2 : d.dof, np1 = k->co.order + 1;
+    const size_t stride = opts->steps_stride ? opts->steps_stride : opts->maxsteps + 1;
+    const size_t cap = opts->event_capacity > 0 ? opts->event_capacity : (size_t)(opts->maxsteps + 1);
+    std::vector<int> rcs(ndev, TB_OK);
+    std::vector<std::string> errs(ndev);
+    std::vector<double> kms(ndev, 0.0);
+    int prev = 0;
+    cudaGetDevice(&prev);
+    auto worker = [&](int di) {
+        if (cudaSetDevice(devices[di]) != cudaSuccess) { rcs[di] = TB_ERR_CUDA; errs[di] = "cudaSetDevice failed"; return; }
+        ShardCopy sc{N, block, di, ndev};
+        const int64_t n = sc.count();
+        if (n == 0) return;
+        std::vector<double> q((size_t)dof * n), par;
+        sc.pack(q0, q.data(), dof, n);
+        const double *pp = params;
+        if (d.npar && opts->params_per_traj) { par.resize((size_t)d.npar * n); sc.pack(params, par.data(), d.npar, n); pp = par.data(); }
+        /* local output buffers for whatever the caller asked for */
+        struct Buf { void *global; void **slot; size_t rows, esz; std::vector<char> mem; };
+        tb_out_t lo;
+        memset(&lo, 0, sizeof lo);
+        std::vector<Buf> bufs;
+        auto want = [&](void *g, void **slot, size_t rows, size_t esz) {
+            if (!g) return;
+            bufs.push_back({g, slot, rows, esz, std::vector<char>(rows * (size_t)n * esz)});
+        };
+        want(out->xfinal, (void **)&lo.xfinal, dof, 8);
+        want(out->tfinal, (void **)&lo.tfinal, 1, 8);
+        want(out->nsteps, (void **)&lo.nsteps, 1, 8);
+        want(out->status, (void **)&lo.status, 1, 4);
+        if (trange) want(out->xv_trange, (void **)&lo.xv_trange, dof * (size_t)nt, 8);
+        else {
+            want(out->tv, (void **)&lo.tv, stride, 8);
+            want(out->xv, (void **)&lo.xv, dof * stride, 8);
+            want(out->psol, (void **)&lo.psol, dof * np1 * stride, 8);
+        }
+        if (k->co.kind == TB_KIND_EVENTS) {
+            want(out->tevents, (void **)&lo.tevents, cap, 8);
+            want(out->xevents, (void **)&lo.xevents, dof * cap, 8);
+            want(out->gresids, (void **)&lo.gresids, cap, 8);
+            want(out->nevents, (void **)&lo.nevents, 1, 4);
+        }
+        if (k->co.kind == TB_KIND_LYAP || lyapcol) {
+            want(out->lambda, (void **)&lo.lambda, dof, 8);
+            want(out->lambda_v, (void **)&lo.lambda_v, trange ? dof * (size_t)nt : dof * stride, 8);
+        }
+        for (auto &b : bufs) *b.slot = b.mem.data();
+        rcs[di] = integrate_host(k, n, q.data(), pp, t0, tmax, trange, nt, opts, &lo);
+        if (rcs[di]) { errs[di] = tb_last_error(); return; }
+        kms[di] = tb_last_kernel_ms();
+        for (auto &b : bufs) {
+            if (b.esz == 8) sc.unpack((double *)b.global, (const double *)b.mem.data(), b.rows, n);
+            else sc.unpack((int32_t *)b.global, (const int32_t *)b.mem.data(), b.rows, n);
+        }
+    };
+    std::vector<std::thread> th;
+    for (int di = 1; di < ndev; di++) th.emplace_back(worker, di);
+    worker(0);
+    for (auto &t : th) t.join();
+    cudaSetDevice(prev);
+    double worst = 0.0;
+    for (int di = 0; di < ndev; di++) {
+        if (rcs[di]) { set_error("tb_integrate_multi: device " + std::to_string(devices[di]) + ": " + errs[di]); return rcs[di]; }
+        worst = std::max(worst, kms[di]);
+    }
+    set_last_kernel_ms(worst); /* the slowest device's kernel */
+    return TB_OK;
+}
+
 size_t tb_work_bytes(void) { return 256; }
 
 int tb_integrate_device(tb_kernel_t *k, int64_t N, const double *d_q0, const double *d_params, double t0, double tmax,
@@ -740,7 +870,7 @@ int tb_jet(tb_kernel_t *k, int64_t N, const double *q0, const double *params, do
     const size_t dof = d.dof, n = (size_t)N, np1 = k->co.order + 1;
     const size_t npar_elems = d.npar ? (opts->params_per_traj ? (size_t)d.npar * n : (size_t)d.npar) : 0;
     if (d.npar > 0 && !params) { set_error("tb_jet: params is NULL"); return TB_ERR_ARG; }
-    std::lock_guard<std::mutex> call_lock(k->call_mu);
+    std::lock_guard<std::mutex> call_lock(device_call_mutex(k));
     Arena A;
     rc = arena_get(k, rup(dof * n * 8) + rup(npar_elems * 8) + rup(dof * np1 * n * 8) + rup(n * 8) + 256, A);
     if (rc) return rc;

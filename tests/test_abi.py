@@ -43,7 +43,7 @@ def test_compiles_for_sm100a_without_gpu():
     k = tb.Kernel(P.kepler_tape(), 28)
     info = k.info()
     assert info["block_threads"] % 32 == 0 and info["smem_bytes"] <= 227 * 1024
-    assert 0 <= info["local_bytes"] <= 232 + 160, "kernel spills more than the bound (232 B is the cold-path array)"
+    assert 0 <= info["local_bytes"] <= 232 + 256, "kernel spills more than the bound (232 B is the cold-path array)"
     assert "tb_ensemble_kernel" in k.source and "sm_100a" in k.log
     assert k.cubin()[:4] == b"\x7fELF"
 
@@ -115,4 +115,4 @@ def test_kernel_info_reports_the_stack_frame():
     k = tb.Kernel(P.kepler_tape(), 28, flags=262144)
     info = k.info()
     assert "bytes stack frame" in k.log
-    assert 0 < info["local_bytes"] <= 232 + 160, info
+    assert 0 < info["local_bytes"] <= 232 + 256, info

@@ -202,3 +202,33 @@ def test_device_entry_point_rejects_what_the_host_entry_point_rejects():
     assert lib.tb_integrate_device(ke.handle, 64, d_q0.data_ptr(), None, 0.0, 1.0, None, 0, C.byref(oe), C.byref(o),
                                    work.data_ptr(), None) == L.TB_ERR_ARG
     torch.cuda.synchronize()
+
+
+def test_integrate_multi_matches_single_device():
+    """tb_integrate_multi (one ensemble over the GPUs of this process, round-robin blocks): same bits as the 1-GPU
+    call whatever the device list.  On a 1-GPU box the list [0, 0] still runs two host threads over two shards."""
+    ndev = L.lib().tb_device_count()
+    devs = list(range(ndev)) if ndev >= 2 else [0, 0]
+    q0, mu, _ = P.kepler_ensemble(10_000)
+    tmax = 2 * np.pi * 2
+    one = tb.taylorinteg(P.kepler_tape(), q0, 0.0, tmax, 28, 1e-20, mu, maxsteps=2000)
+    for block in (4096, 1000, 7):
+        m = tb.taylorinteg(P.kepler_tape(), q0, 0.0, tmax, 28, 1e-20, mu, maxsteps=2000, devices=devs, block=block)
+        _same(m, one)
+    pq = P.pendulum_ensemble(3000)
+    one = tb.taylorinteg_events(P.pendulum_tape(), pq, 0.0, 20.0, 25, 1e-20, maxsteps=1000, event_capacity=16, output="final")
+    m = tb.taylorinteg_events(P.pendulum_tape(), pq, 0.0, 20.0, 25, 1e-20, maxsteps=1000, event_capacity=16, output="final",
+                              devices=devs, block=512)
+    _same(m, one)
+    assert np.array_equal(m.nevents, one.nevents)
+    mask = np.arange(16)[:, None] < one.nevents[None, :]
+    assert np.array_equal(m.tevents[mask], one.tevents[mask]) and np.array_equal(m.xevents[:, mask], one.xevents[:, mask])
+    lq, par = P.lorenz_ensemble(700)
+    one = tb.lyap_taylorinteg(P.lorenz_tape(), lq, 0.0, 1.0, 28, 1e-20, par, maxsteps=2000)
+    m = tb.lyap_taylorinteg(P.lorenz_tape(), lq, 0.0, 1.0, 28, 1e-20, par, maxsteps=2000, devices=devs, block=64)
+    _same(m, one)
+    assert np.array_equal(m.lam, one.lam)
+    tr = np.linspace(0.0, 3.0, 13)
+    one = tb.taylorinteg(P.kepler_tape(), q0[:, :900], tr, 28, 1e-20, mu)
+    m = tb.taylorinteg(P.kepler_tape(), q0[:, :900], tr, 28, 1e-20, mu, devices=devs, block=100)
+    assert np.array_equal(m.x_trange, one.x_trange)
