@@ -46,6 +46,15 @@ struct Math {
     double pow_(double x, double y) const { return mode == MATH_TB ? tb_pow(x, y) : std::pow(x, y); }
     double exp_(double x) const { return mode == MATH_TB ? tb_exp(x) : std::exp(x); }
     double log_(double x) const { return mode == MATH_TB ? tb_log(x) : std::log(x); }
+    double tan_(double x) const { return mode == MATH_TB ? tb_tan(x) : std::tan(x); }
+    double tanh_(double x) const { return mode == MATH_TB ? tb_tanh(x) : std::tanh(x); }
+    double atan_(double x) const { return mode == MATH_TB ? tb_atan(x) : std::atan(x); }
+    double asin_(double x) const { return mode == MATH_TB ? tb_asin(x) : std::asin(x); }
+    double acos_(double x) const { return mode == MATH_TB ? tb_acos(x) : std::acos(x); }
+    void sinhcosh_(double x, double *s, double *c) const {
+        if (mode == MATH_TB) tb_sinhcosh(x, s, c);
+        else { *s = std::sinh(x); *c = std::cosh(x); }
+    }
     void sincos_(double x, double *s, double *c) const {
         if (mode == MATH_TB) tb_sincos(x, s, c);
         else { *s = std::sin(x); *c = std::cos(x); }
@@ -179,6 +188,55 @@ inline void p_sincos(const Math &m, double *s, double *c, const double *a, int k
     c[k] = ck / k;
 }
 
+/* ---- primitives with an auxiliary series (src/parse_eqs.jl:1013-1046): tan!, tanh! (aux = c^2), atan! (aux = 1 + a^2),
+ * asin!, acos! (aux = sqrt(1 - a^2)), sinhcosh! (aux = the companion).  TaylorSeries.jl recurrences (external, recalled
+ * like the rest of App. B; checked against closed-form Taylor coefficients in tests/test_primitives.py).        */
+/* tan!(c, a, c2, k): c[k] = a[k] + (sum_{i<k} (k-i) a[k-i] c2[i]) / k; then sqr!(c2, c, k) */
+inline void p_tan(const Math &m, double *c, double *c2, const double *a, int k, bool hyp) {
+    if (k == 0) { c[0] = hyp ? m.tanh_(a[0]) : m.tan_(a[0]); c2[0] = c[0] * c[0]; return; }
+    double s = k * a[k] * c2[0];
+    for (int i = 1; i <= k - 1; i++) s += (k - i) * a[k - i] * c2[i];
+    c[k] = hyp ? a[k] - s / k : a[k] + s / k;
+    c2[k] = p_sqr(c, k);
+}
+/* sinhcosh!(s, c, a, k) */
+inline void p_sinhcosh(const Math &m, double *s, double *c, const double *a, int k) {
+    if (k == 0) { m.sinhcosh_(a[0], &s[0], &c[0]); return; }
+    double x = a[1];
+    double sk = x * c[k - 1], ck = x * s[k - 1];
+    for (int i = 2; i <= k; i++) {
+        x = i * a[i];
+        sk += x * c[k - i];
+        ck += x * s[k - i];
+    }
+    s[k] = sk / k;
+    c[k] = ck / k;
+}
+/* atan!(c, a, r, k): r = 1 + a^2;  c[k] = (a[k] - (sum_{i=1..k-1} (k-i) r[i] c[k-i]) / k) / r[0] */
+inline void p_atan(const Math &m, double *c, double *r, const double *a, int k) {
+    if (k == 0) { c[0] = m.atan_(a[0]); r[0] = 1 + a[0] * a[0]; return; }
+    double s = (k - 1) * r[1] * c[k - 1];
+    for (int i = 2; i <= k - 1; i++) s += (k - i) * r[i] * c[k - i];
+    r[k] = p_sqr(a, k);
+    c[k] = (a[k] - s / k) / r[0];
+}
+/* asin!(c, a, r, k) / acos!: r = sqrt(1 - a^2), r[k] from sqrt!(r, 1 - a^2, k) */
+inline void p_asin(const Math &m, double *c, double *r, const double *a, int k, bool is_acos) {
+    if (k == 0) { c[0] = is_acos ? m.acos_(a[0]) : m.asin_(a[0]); r[0] = std::sqrt(1 - a[0] * a[0]); return; }
+    double s = (k - 1) * r[1] * c[k - 1];
+    for (int i = 2; i <= k - 1; i++) s += (k - i) * r[i] * c[k - i];
+    {   /* sqrt!(r, 1 - a^2, k): coefficient k of 1 - a^2 is -(a^2)[k] */
+        const double ak = -p_sqr(a, k);
+        const int kodd = k % 2, kend = (k - 2 + kodd) / 2;
+        double q = 0.0;
+        for (int i = 1; i <= kend; i++) { if (i == 1) q = r[i] * r[k - i]; else q += r[i] * r[k - i]; }
+        double aux = ak - 2 * q;
+        if (kodd == 0) aux -= r[kend + 1] * r[kend + 1];
+        r[k] = aux / (2 * r[0]);
+    }
+    c[k] = is_acos ? -(a[k] + s / k) / r[0] : (a[k] - s / k) / r[0];
+}
+
 int run_op(Work &w, const tb_op_t &op, int k) {
     double *res = w.series(op.res);
     if (!res) return TB_ERR_ARG;
@@ -233,6 +291,15 @@ int run_op(Work &w, const tb_op_t &op, int k) {
             double *cs = w.series(op.aux);
             if (!cs) return TB_ERR_ARG;
             p_sincos(w.math, res, cs, a, k);
+            break;
+        }
+        case TB_OP_TAN: case TB_OP_TANH: case TB_OP_ATAN: case TB_OP_ASIN: case TB_OP_ACOS: case TB_OP_SINHCOSH: {
+            double *ax = w.series(op.aux);
+            if (!ax || !a) return TB_ERR_ARG;
+            if (op.op == TB_OP_TAN || op.op == TB_OP_TANH) p_tan(w.math, res, ax, a, k, op.op == TB_OP_TANH);
+            else if (op.op == TB_OP_ATAN) p_atan(w.math, res, ax, a, k);
+            else if (op.op == TB_OP_SINHCOSH) p_sinhcosh(w.math, res, ax, a, k);
+            else p_asin(w.math, res, ax, a, k, op.op == TB_OP_ACOS);
             break;
         }
         default: return TB_ERR_UNSUPPORTED;
@@ -753,6 +820,12 @@ void tbo_math_pow_pair(double x1, double y1, double x2, double y2, double *r) { 
 double tbo_math_exp(double x) { return tb_exp(x); }
 double tbo_math_log(double x) { return tb_log(x); }
 void tbo_math_sincos(double x, double *s, double *c) { tb_sincos(x, s, c); }
+double tbo_math_tan(double x) { return tb_tan(x); }
+double tbo_math_tanh(double x) { return tb_tanh(x); }
+double tbo_math_atan(double x) { return tb_atan(x); }
+double tbo_math_asin(double x) { return tb_asin(x); }
+double tbo_math_acos(double x) { return tb_acos(x); }
+void tbo_math_sinhcosh(double x, double *s, double *c) { tb_sinhcosh(x, s, c); }
 
 /* First step: jets x[dof x (P+1)] (row per component), dx likewise, and dt.
  * kind = TB_KIND_LYAP is not supported here (use tbo_integrate).              */

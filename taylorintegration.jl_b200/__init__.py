@@ -5,7 +5,8 @@ identifier; import it through the repo-root shim `taylorintegration_b200`.
 """
 from . import _lib  # noqa: F401
 from ._lib import TaylorB200Error  # noqa: F401
-from .tape import Tape, taylorize, sin, cos, sqrt, exp, log, zero  # noqa: F401
+from .tape import (Tape, taylorize, sin, cos, sqrt, exp, log, zero, tan, sinh, cosh, tanh, atan, asin,  # noqa: F401
+                   acos)
 from .api import (EnsembleSolution, Kernel, TaylorSolution, fp64_peak, get_kernel, lyap_taylorinteg, make_opts,  # noqa: F401
                   taylorinteg, taylorinteg_events)
 from .jettransport import JetSolution, JetTransport, taylorinteg_jet  # noqa: F401

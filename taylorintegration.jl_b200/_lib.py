@@ -23,7 +23,8 @@ OP_EXP, OP_LOG, OP_SINCOS, OP_ZERO, OP_ONE, OP_TAN, OP_SINHCOSH, OP_TANH, OP_ATA
 OP_NAMES = {
     OP_IDENTITY: "identity!", OP_NEG: "subst!(neg)", OP_ADD: "add!", OP_SUB: "subst!", OP_MUL: "mul!", OP_DIV: "div!",
     OP_SQR: "sqr!", OP_SQRT: "sqrt!", OP_POW: "pow!", OP_EXP: "exp!", OP_LOG: "log!", OP_SINCOS: "sincos!",
-    OP_ZERO: "zero!", OP_ONE: "one!",
+    OP_ZERO: "zero!", OP_ONE: "one!", OP_TAN: "tan!", OP_SINHCOSH: "sinhcosh!", OP_TANH: "tanh!", OP_ATAN: "atan!",
+    OP_ASIN: "asin!", OP_ACOS: "acos!",
 }
 K_NONE, K_X, K_DX, K_TMP, K_PAR, K_TIME, K_IMM = range(7)
 JAC_ZERO, JAC_CONST, JAC_SERIES, JAC_PAR = range(4)
@@ -86,7 +87,7 @@ class TbOut(C.Structure):
 
 EXPORTS = [
     "tb_abi_version", "tb_last_error", "tb_ode_create", "tb_ode_free", "tb_opts_default", "tb_compile_opts_default",
-    "tb_generate_source", "tb_compile", "tb_integrate_multi", "tb_kernel_free", "tb_kernel_source", "tb_kernel_log", "tb_kernel_info",
+    "tb_generate_source", "tb_compile", "tb_integrate_multi", "tb_wide_layout", "tb_kernel_free", "tb_kernel_source", "tb_kernel_log", "tb_kernel_info",
     "tb_kernel_cubin", "tb_integrate", "tb_integrate_trange", "tb_work_bytes", "tb_integrate_device",
     "tb_launch_count", "tb_jet", "tb_dense_eval", "tb_fp64_peak", "tb_device_count", "tb_set_device",
     "tb_tn_create", "tb_tn_free", "tb_tn_ncoef", "tb_tn_monomials", "tb_tn_integrate",
@@ -160,6 +161,7 @@ def lib() -> C.CDLL:
     L.tb_wide_create.argtypes = [vp, C.c_int, C.c_int]
     L.tb_wide_free.argtypes = [vp]
     L.tb_wide_info.argtypes = [vp] + [C.POINTER(C.c_int)] * 4
+    L.tb_wide_layout.argtypes = [vp] + [C.POINTER(C.c_int)] * 6
     L.tb_wide_integrate.argtypes = [vp, C.c_int64, vp, vp, C.c_double, C.c_double, vp, C.c_int64, C.POINTER(TbOpts),
                                     C.POINTER(TbOut)]
     _lib = L

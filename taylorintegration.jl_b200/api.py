@@ -134,7 +134,12 @@ class WideKernel:
     def info(self) -> Dict[str, int]:
         v = [C.c_int(-1) for _ in range(4)]
         L.lib().tb_wide_info(self._w, *[C.byref(x) for x in v])
-        return dict(zip(["entries", "levels", "series", "max_width"], [x.value for x in v]))
+        d = dict(zip(["entries", "levels", "series", "max_width"], [x.value for x in v]))
+        v2 = [C.c_int(-1) for _ in range(6)]
+        if L.lib().tb_wide_layout(self._w, *[C.byref(x) for x in v2]) == 0:  # the shared-memory cluster kernel applies
+            d.update(zip(["clusters", "stored_series", "scalar_slots", "threads", "smem_bytes", "ctas_per_sm"],
+                         [x.value for x in v2]))
+        return d
 
 
 def is_wide(tape: Tape) -> bool:

@@ -61,7 +61,9 @@ void index_reads(const tb_op_t &op, std::vector<int32_t> &out) {
             else if (op.imm != 0.0 && op.imm != 1.0) { out.push_back(op.a); out.push_back(op.res); }
             break;
         case TB_OP_EXP: case TB_OP_LOG: out.push_back(op.a); out.push_back(op.res); break;
-        case TB_OP_SINCOS: out.push_back(op.a); out.push_back(op.res); out.push_back(op.aux); break;
+        case TB_OP_SINCOS: case TB_OP_SINHCOSH: out.push_back(op.a); out.push_back(op.res); out.push_back(op.aux); break;
+        case TB_OP_TAN: case TB_OP_TANH: case TB_OP_ATAN: case TB_OP_ASIN: case TB_OP_ACOS:
+            out.push_back(op.a); out.push_back(op.res); out.push_back(op.aux); break;
         default: break;
     }
 }
@@ -105,7 +107,7 @@ struct Gen {
                         if (is_series(o) && !produced.count(o)) mark(o);
                 }
                 produced.insert(op.res);
-                if (op.op == TB_OP_SINCOS) produced.insert(op.aux);
+                if (op.op == TB_OP_SINCOS || (op.op >= TB_OP_TAN && op.op <= TB_OP_ACOS)) produced.insert(op.aux);
             }
         }
         if (co.kind == TB_KIND_EVENTS) {
@@ -267,6 +269,72 @@ struct Gen {
                 defined.insert(op.aux);
                 break;
             }
+            case TB_OP_SINHCOSH: { /* sinhcosh!(s, c, a, k) */
+                const std::string rc = vname(op.aux);
+                if (k0) e.line("  tb_sinhcosh(%s, &%s, &%s);", A, R, rc.c_str());
+                else {
+                    e.line("  { double x = %s;", at(op.a, "1").c_str());
+                    e.line("    double sk = M_(x, %s), ck = M_(x, %s);", at(op.aux, "k - 1").c_str(), at(op.res, "k - 1").c_str());
+                    e.line("    for (int i = 2; i <= k; i++) { x = M_((double)i, %s);", at(op.a, "i").c_str());
+                    e.line("      sk = A_(sk, M_(x, %s)); ck = A_(ck, M_(x, %s)); }", at(op.aux, "k - i").c_str(), at(op.res, "k - i").c_str());
+                    e.line("    %s = D_(sk, (double)k); %s = D_(ck, (double)k); }", R, rc.c_str());
+                }
+                e.line("  %s = %s;", at(op.aux, k0 ? "0" : "k").c_str(), rc.c_str());
+                defined.insert(op.aux);
+                break;
+            }
+            case TB_OP_TAN: case TB_OP_TANH: { /* tan!(c, a, c2, k), tanh!(c, a, c2, k): aux = c^2 */
+                const std::string rc = vname(op.aux);
+                const bool hyp = opc == TB_OP_TANH;
+                if (k0) { e.line("  %s = %s(%s);", R, hyp ? "tb_tanh" : "tb_tan", A); e.line("  %s = M_(%s, %s);", rc.c_str(), R, R); }
+                else {
+                    e.line("  { double s = M_(M_((double)k, %s), %s);", A, at(op.aux, "0").c_str());
+                    e.line("    for (int i = 1; i <= k - 1; i++) s = A_(s, M_(M_((double)(k - i), %s), %s));", at(op.a, "k - i").c_str(), at(op.aux, "i").c_str());
+                    e.line("    %s = %s(%s, D_(s, (double)k)); }", R, hyp ? "B_" : "A_", A);
+                    /* sqr!(c2, c, k) with c[k] = the value just computed */
+                    e.line("  { const int kodd = k & 1, kend = (k - 2 + kodd) / 2;");
+                    e.line("    double c = M_(%s, %s);", at(op.res, "0").c_str(), R);
+                    e.line("    for (int i = 1; i <= kend; i++) c = A_(c, M_(%s, %s));", at(op.res, "i").c_str(), at(op.res, "k - i").c_str());
+                    e.line("    c = M_(2.0, c);");
+                    e.line("    if (!kodd) { const double h = %s; c = A_(c, M_(h, h)); }", at(op.res, "k >> 1").c_str());
+                    e.line("    %s = c; }", rc.c_str());
+                }
+                e.line("  %s = %s;", at(op.aux, k0 ? "0" : "k").c_str(), rc.c_str());
+                defined.insert(op.aux);
+                break;
+            }
+            case TB_OP_ATAN: case TB_OP_ASIN: case TB_OP_ACOS: { /* aux r = 1 + a^2 (atan!) or sqrt(1 - a^2) (asin!, acos!) */
+                const std::string rc = vname(op.aux);
+                if (k0) {
+                    e.line("  %s = %s(%s);", R, opc == TB_OP_ATAN ? "tb_atan" : (opc == TB_OP_ASIN ? "tb_asin" : "tb_acos"), A);
+                    if (opc == TB_OP_ATAN) e.line("  %s = A_(1.0, M_(%s, %s));", rc.c_str(), A, A);
+                    else e.line("  %s = Q_(B_(1.0, M_(%s, %s)));", rc.c_str(), A, A);
+                } else {
+                    e.line("  { double s = 0.0;");
+                    e.line("    if (k >= 2) s = M_(M_((double)(k - 1), %s), %s);", at(op.aux, "1").c_str(), at(op.res, "k - 1").c_str());
+                    e.line("    for (int i = 2; i <= k - 1; i++) s = A_(s, M_(M_((double)(k - i), %s), %s));", at(op.aux, "i").c_str(), at(op.res, "k - i").c_str());
+                    /* (a^2)[k] by sqr! */
+                    e.line("    const int kodd = k & 1, kend = (k - 2 + kodd) / 2;");
+                    e.line("    double c = M_(%s, %s);", at(op.a, "0").c_str(), A);
+                    e.line("    for (int i = 1; i <= kend; i++) c = A_(c, M_(%s, %s));", at(op.a, "i").c_str(), at(op.a, "k - i").c_str());
+                    e.line("    c = M_(2.0, c);");
+                    e.line("    if (!kodd) { const double h = %s; c = A_(c, M_(h, h)); }", at(op.a, "k >> 1").c_str());
+                    if (opc == TB_OP_ATAN) e.line("    %s = c;", rc.c_str());
+                    else { /* sqrt!(r, 1 - a^2, k) */
+                        e.line("    double q = 0.0;");
+                        e.line("    if (kend >= 1) q = M_(%s, %s);", at(op.aux, "1").c_str(), at(op.aux, "k - 1").c_str());
+                        e.line("    for (int i = 2; i <= kend; i++) q = A_(q, M_(%s, %s));", at(op.aux, "i").c_str(), at(op.aux, "k - i").c_str());
+                        e.line("    double aux = B_(N_(c), M_(2.0, q));");
+                        e.line("    if (!kodd) { const double h = %s; aux = B_(aux, M_(h, h)); }", at(op.aux, "kend + 1").c_str());
+                        e.line("    %s = D_(aux, M_(2.0, %s));", rc.c_str(), at(op.aux, "0").c_str());
+                    }
+                    if (opc == TB_OP_ACOS) e.line("    %s = D_(N_(A_(%s, D_(s, (double)k))), %s); }", R, A, at(op.aux, "0").c_str());
+                    else e.line("    %s = D_(B_(%s, D_(s, (double)k)), %s); }", R, A, at(op.aux, "0").c_str());
+                }
+                e.line("  %s = %s;", at(op.aux, k0 ? "0" : "k").c_str(), rc.c_str());
+                defined.insert(op.aux);
+                break;
+            }
             default: err = "opcode not supported by the code generator"; break;
         }
         if (slot_of(op.res) >= 0) e.line("  %s = %s;", at(op.res, k0 ? "0" : "k").c_str(), R);
@@ -281,7 +349,7 @@ struct Gen {
         std::set<int32_t> vars;
         for (int j = first; j < first + count; j++) {
             vars.insert(ode.ops[j].res);
-            if (ode.ops[j].op == TB_OP_SINCOS) vars.insert(ode.ops[j].aux);
+            if (ode.ops[j].op == TB_OP_SINCOS || (ode.ops[j].op >= TB_OP_TAN && ode.ops[j].op <= TB_OP_ACOS)) vars.insert(ode.ops[j].aux);
         }
         for (int32_t v : vars) e.line("  double %s;", vname(v).c_str());
         std::set<int32_t> defined;

@@ -886,6 +886,11 @@ int generate_unrolled(const Ode &ode, const tb_compile_opts_t &co, Layout &L, st
         return TB_ERR_ARG;
     }
     if (d.dof > 16 || d.nops > 200) { err = "tape too large to unroll"; return TB_ERR_UNSUPPORTED; }
+    for (int j = 0; j < d.nops; j++)
+        if (ode.ops[j].op >= TB_OP_TAN && ode.ops[j].op <= TB_OP_ACOS) {
+            err = "tan!/sinhcosh!/tanh!/atan!/asin!/acos! are lowered by the rolled generator";
+            return TB_ERR_UNSUPPORTED;
+        }
     std::set<int32_t> seen;
     for (int j = 0; j < d.nops; j++) {
         const tb_op_t &op = ode.ops[j];

@@ -161,9 +161,9 @@ static int arity_ok(const tb_op_t &op, std::string &why) {
              * method throw in the reference too (test/taylorize.jl:953-992)       */
             if (!series(op.a)) { why = "unary Taylor primitive needs a series argument"; return 0; }
             break;
-        case TB_OP_SINCOS:
-            if (!series(op.a)) { why = "sincos! needs a series argument"; return 0; }
-            if (kind(op.aux) != TB_K_TMP && kind(op.aux) != TB_K_DX) { why = "sincos! needs an auxiliary series"; return 0; }
+        case TB_OP_SINCOS: case TB_OP_TAN: case TB_OP_SINHCOSH: case TB_OP_TANH: case TB_OP_ATAN: case TB_OP_ASIN: case TB_OP_ACOS:
+            if (!series(op.a)) { why = "primitive with an auxiliary series needs a series argument"; return 0; }
+            if (kind(op.aux) != TB_K_TMP && kind(op.aux) != TB_K_DX) { why = "sincos!/tan!/tanh!/atan!/asin!/acos!/sinhcosh! need an auxiliary series"; return 0; }
             break;
         case TB_OP_ADD: case TB_OP_SUB: case TB_OP_MUL: case TB_OP_DIV:
             if (!(series(op.a) || number(op.a)) || !(series(op.b) || number(op.b))) { why = "binary op needs two arguments"; return 0; }

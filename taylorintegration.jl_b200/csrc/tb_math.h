@@ -331,4 +331,78 @@ TB_HD void tb_sincos(double x, double *sn, double *cs) {
     }
 }
 
+
+/* ---- tan, sinh/cosh, tanh, atan, asin, acos: seeds of tan!, sinhcosh!, tanh!, atan!, asin!, acos! at k = 0 -------
+ * Same contract as above (IEEE operations in a fixed order, identical on host and device); accuracy a few ulp
+ * (tests/test_math.py), which is what the order-0 coefficient of these recurrences inherits.                    */
+TB_HD double tb_tan(double x) { double s, c; tb_sincos(x, &s, &c); return TB_DIV(s, c); }
+TB_HD void tb_sinhcosh(double x, double *sh, double *ch) {
+    const double ax = TB_ABS(x);
+    const double e = tb_exp(ax), ei = TB_DIV(1.0, e);
+    *ch = TB_MUL(0.5, TB_ADD(e, ei));
+    double s;
+    if (ax < 0.5) { /* odd Taylor polynomial: no cancellation */
+        const double z = TB_MUL(ax, ax);
+        double p = 1.0 / 1307674368000.0;
+        p = TB_FMA(p, z, 1.0 / 6227020800.0);
+        p = TB_FMA(p, z, 1.0 / 39916800.0);
+        p = TB_FMA(p, z, 1.0 / 362880.0);
+        p = TB_FMA(p, z, 1.0 / 5040.0);
+        p = TB_FMA(p, z, 1.0 / 120.0);
+        p = TB_FMA(p, z, 1.0 / 6.0);
+        s = TB_FMA(TB_MUL(ax, z), p, ax);
+    } else s = TB_MUL(0.5, TB_SUB(e, ei));
+    *sh = x < 0.0 ? -s : s;
+}
+TB_HD double tb_tanh(double x) {
+    if (TB_ABS(x) > 22.0) return x < 0.0 ? -1.0 : 1.0;
+    double s, c;
+    tb_sinhcosh(x, &s, &c);
+    return TB_DIV(s, c);
+}
+/* atan: |x| > 1 -> pi/2 - atan(1/x); t = c + u with c = j/8: atan(t) = atan(c) + atan((t - c)/(1 + t c)), |u'| <= 1/16 */
+TB_HD double tb_atan(double x) {
+    if (x != x) return x;
+    const double ax = TB_ABS(x);
+    const bool inv = ax > 1.0;
+    const double t = inv ? TB_DIV(1.0, ax) : ax;
+    const int j = (int)TB_ADD(TB_MUL(8.0, t), 0.5);
+    const double c = TB_MUL(0.125, (double)j);
+    const double u = TB_DIV(TB_SUB(t, c), TB_FMA(t, c, 1.0));
+    const double z = TB_MUL(u, u);
+    double p = 1.0 / 15.0;
+    p = TB_FMA(TB_MUL(-1.0, p), z, 1.0 / 13.0);
+    p = TB_FMA(TB_MUL(-1.0, p), z, 1.0 / 11.0);
+    p = TB_FMA(TB_MUL(-1.0, p), z, 1.0 / 9.0);
+    p = TB_FMA(TB_MUL(-1.0, p), z, 1.0 / 7.0);
+    p = TB_FMA(TB_MUL(-1.0, p), z, 1.0 / 5.0);
+    p = TB_FMA(TB_MUL(-1.0, p), z, 1.0 / 3.0);
+    const double au = TB_FMA(TB_MUL(TB_MUL(-1.0, u), z), p, u); /* u - u^3/3 + u^5/5 - ... */
+    double hi, lo;
+    switch (j) {
+        case 0: hi = TB_FROM_BITS(0x0000000000000000ULL); lo = TB_FROM_BITS(0x0000000000000000ULL); break;
+        case 1: hi = TB_FROM_BITS(0x3fbfd5ba9aac2f6eULL); lo = TB_FROM_BITS(0xbc4cd37686760c17ULL); break;
+        case 2: hi = TB_FROM_BITS(0x3fcf5b75f92c80ddULL); lo = TB_FROM_BITS(0x3c68ab6e3cf7afbdULL); break;
+        case 3: hi = TB_FROM_BITS(0x3fd6f61941e4def1ULL); lo = TB_FROM_BITS(0xbc7c63aae6f6e918ULL); break;
+        case 4: hi = TB_FROM_BITS(0x3fddac670561bb4fULL); lo = TB_FROM_BITS(0x3c7a2b7f222f65e2ULL); break;
+        case 5: hi = TB_FROM_BITS(0x3fe1e00babdefeb4ULL); lo = TB_FROM_BITS(0xbc5928df287a668fULL); break;
+        case 6: hi = TB_FROM_BITS(0x3fe4978fa3269ee1ULL); lo = TB_FROM_BITS(0x3c72419a87f2a458ULL); break;
+        case 7: hi = TB_FROM_BITS(0x3fe700a7c5784634ULL); lo = TB_FROM_BITS(0xbc78c34d25aadef6ULL); break;
+        case 8: hi = TB_FROM_BITS(0x3fe921fb54442d18ULL); lo = TB_FROM_BITS(0x3c81a62633145c07ULL); break;
+        default: hi = 0.0; lo = 0.0; break;
+    }
+    double r = TB_ADD(hi, TB_ADD(lo, au));
+    if (inv) r = TB_ADD(TB_FROM_BITS(0x3ff921fb54442d18ULL), TB_SUB(TB_FROM_BITS(0x3c91a62633145c07ULL), r));
+    return x < 0.0 ? -r : r;
+}
+TB_HD double tb_asin(double x) {
+    const double ax = TB_ABS(x);
+    if (ax == 1.0) return x < 0.0 ? -TB_FROM_BITS(0x3ff921fb54442d18ULL) : TB_FROM_BITS(0x3ff921fb54442d18ULL);
+    return tb_atan(TB_DIV(x, TB_SQRT(TB_MUL(TB_SUB(1.0, ax), TB_ADD(1.0, ax)))));
+}
+TB_HD double tb_acos(double x) {
+    if (x == -1.0) return TB_MUL(2.0, TB_FROM_BITS(0x3ff921fb54442d18ULL));
+    return TB_MUL(2.0, tb_atan(TB_SQRT(TB_DIV(TB_SUB(1.0, x), TB_ADD(1.0, x)))));
+}
+
 #endif /* TB_MATH_H */

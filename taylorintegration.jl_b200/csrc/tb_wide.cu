@@ -21,6 +21,7 @@
 
 #include "tb_internal.h"
 #include "tb_math.h"
+#include "tb_wide_prog.h"
 
 namespace tb {
 void count_launch(long long n);
@@ -41,16 +42,8 @@ namespace {
         }                                                                      \
     } while (0)
 
-enum { W_LINCOMB = 100 };
-
-/* internal tape entry: operands are compact series ids (>= 0) or -1 for a number */
-struct WOp {
-    int op, res, a, b, aux;
-    int para, parb; /* parameter index of a numeric operand, -1 = immediate */
-    double imma, immb;
-    double imm;     /* pow! exponent */
-    int lc_off, lc_n, lc_stride; /* term j of the chain at lc_off + j*lc_stride (chains of a level interleaved: coalesced) */
-};
+using tbw::WOp;
+using tbw::W_LINCOMB;
 
 struct WArgs {
     long long N;
@@ -370,6 +363,8 @@ struct tb_wide {
     WOp *d_ops = nullptr;
     int *d_lev = nullptr, *d_lcs = nullptr, *d_xs = nullptr, *d_dxs = nullptr;
     double *d_lcc = nullptr;
+    tbw::Wide2 *v2 = nullptr;  /* cluster kernel with jets in shared memory (tb_wide2.cu); null when it does not apply */
+    std::string v2_why;
 };
 
 static bool w_num(int32_t o) { int k = TB_OPERAND_KIND(o); return k == TB_K_PAR || k == TB_K_IMM; }
@@ -491,6 +486,14 @@ tb_wide_t *tb_wide_create(const tb_ode_t *ode, int order, int mode) {
     w->lev_off.assign(nlev + 1, 0);
     for (int L : level) w->lev_off[L + 1]++;
     for (int l = 0; l < nlev; l++) { w->maxwidth = std::max(w->maxwidth, w->lev_off[l + 1]); w->lev_off[l + 1] += w->lev_off[l]; }
+    {   /* the same fused program, in tape order, for the shared-memory cluster kernel */
+        tbw::Program pg;
+        pg.order = order; pg.mode = mode; pg.dof = d.dof; pg.npar = d.npar; pg.nser = w->nser; pg.tser = w->tser;
+        pg.ops = prog;
+        for (tbw::WOp &o : pg.ops) o.lc_stride = 1;
+        pg.lc_coef = w->lc_coef; pg.lc_ser = w->lc_ser; pg.xser = w->xser; pg.dxser = w->dxser;
+        w->v2 = tbw::wide2_build(pg, w->v2_why);
+    }
     w->ops.resize(prog.size());
     std::vector<int> fill(w->lev_off.begin(), w->lev_off.end() - 1);
     for (size_t j = 0; j < prog.size(); j++) w->ops[fill[level[j]]++] = prog[j]; /* stable inside a level */
@@ -525,6 +528,7 @@ tb_wide_t *tb_wide_create(const tb_ode_t *ode, int order, int mode) {
 void tb_wide_free(tb_wide_t *w) {
     if (!w) return;
     if (w->d_ops) { cudaFree(w->d_ops); cudaFree(w->d_lev); cudaFree(w->d_lcs); cudaFree(w->d_xs); cudaFree(w->d_dxs); cudaFree(w->d_lcc); }
+    tbw::wide2_free(w->v2);
     delete w;
 }
 
@@ -538,11 +542,23 @@ int tb_wide_info(const tb_wide_t *w, int *nops, int *nlev, int *nser, int *maxwi
     return TB_OK;
 }
 
+/* layout of the shared-memory cluster kernel; TB_ERR_UNSUPPORTED (reason in tb_last_error) when it does not apply */
+int tb_wide_layout(const tb_wide_t *w, int *nclusters, int *npersistent, int *ntransient, int *threads, int *smem_bytes, int *ctas_per_sm) {
+    if (!w) return TB_ERR_ARG;
+    if (!w->v2) { tb::set_error("tb_wide_layout: " + w->v2_why); return TB_ERR_UNSUPPORTED; }
+    tbw::wide2_info(w->v2, nclusters, npersistent, ntransient, threads, smem_bytes, ctas_per_sm);
+    return TB_OK;
+}
+
 int tb_wide_integrate(tb_wide_t *w, int64_t N, const double *q0, const double *params, double t0, double tmax,
                       const double *trange, int64_t nt, const tb_opts_t *o, const tb_out_t *out) {
     if (!w || !q0 || !o || !out || N < 0 || (trange && nt < 2)) { tb::set_error("tb_wide_integrate: bad argument"); return TB_ERR_ARG; }
     if (out->tv || out->xv || out->psol || out->tevents || out->lambda) { tb::set_error("tb_wide_integrate: only xfinal/tfinal/nsteps/status/xv_trange outputs"); return TB_ERR_UNSUPPORTED; }
     if (N == 0) return TB_OK;
+    if (w->npar > 0 && !params) { tb::set_error("tb_wide_integrate: params is NULL"); return TB_ERR_ARG; }
+    /* jets in shared memory when the stored series fit (tb_wide2.cu); TB_WIDE_V1=1 forces the global-workspace kernel */
+    const char *v1 = getenv("TB_WIDE_V1");
+    if (w->v2 && !(v1 && v1[0] == '1')) return tbw::wide2_integrate(w->v2, N, q0, params, t0, tmax, trange, nt, o, out);
     int dev = 0, nsm = 148;
     TB_CUDA(cudaGetDevice(&dev));
     TB_CUDA(cudaDeviceGetAttribute(&nsm, cudaDevAttrMultiProcessorCount, dev));

@@ -233,7 +233,7 @@ class _DxVector:
         last = tr.ops[-1] if tr.ops else None
         if v.kind == L.K_TMP and last is not None and last.res == v.operand:
             last.res = target
-        elif v.kind == L.K_TMP and last is not None and last.aux == v.operand and last.op == L.OP_SINCOS:
+        elif v.kind == L.K_TMP and last is not None and last.aux == v.operand and last.op in (L.OP_SINCOS, L.OP_SINHCOSH):
             last.aux = target
         else:
             o = Op(L.OP_IDENTITY, target, v.operand)
@@ -241,6 +241,10 @@ class _DxVector:
                 o.imm = v.value
             tr.ops.append(o)
         self.assigned[i] = True
+
+
+# primitives that carry an auxiliary series (src/parse_eqs.jl:1013-1046)
+_AUX_OPS = (L.OP_SINCOS, L.OP_TAN, L.OP_SINHCOSH, L.OP_TANH, L.OP_ATAN, L.OP_ASIN, L.OP_ACOS)
 
 
 def _unary(op: int, fallback: Callable[[float], float], pick_aux: bool = False):
@@ -253,7 +257,7 @@ def _unary(op: int, fallback: Callable[[float], float], pick_aux: bool = False):
             return Val(x.tr, L.K_IMM, 0, fallback(x.value))
         if x.is_number:
             raise TypeError("Taylor primitive needs a series argument; promote the scalar with `+ zero(t)`")
-        o = x.tr.emit(op, x, aux=(op == L.OP_SINCOS))
+        o = x.tr.emit(op, x, aux=(op in _AUX_OPS))
         return Val.from_operand(x.tr, o.aux if pick_aux else o.res)
     return fn
 
@@ -263,6 +267,13 @@ cos = _unary(L.OP_SINCOS, math.cos, pick_aux=True)
 sqrt = _unary(L.OP_SQRT, math.sqrt)
 exp = _unary(L.OP_EXP, math.exp)
 log = _unary(L.OP_LOG, math.log)
+tan = _unary(L.OP_TAN, math.tan)        # tan!(c, a, c2, k), aux = tan(a)^2
+sinh = _unary(L.OP_SINHCOSH, math.sinh)  # sinhcosh!(s, c, a, k)
+cosh = _unary(L.OP_SINHCOSH, math.cosh, pick_aux=True)
+tanh = _unary(L.OP_TANH, math.tanh)
+atan = _unary(L.OP_ATAN, math.atan)      # aux = 1 + a^2
+asin = _unary(L.OP_ASIN, math.asin)      # aux = sqrt(1 - a^2)
+acos = _unary(L.OP_ACOS, math.acos)
 
 
 def zero(x) -> float:

@@ -81,3 +81,35 @@ def test_gpu_wide_interpreter_matches_thread_kernel():
     assert np.array_equal(c.nsteps, rp.nsteps) and np.array_equal(c.xfinal, rp.xfinal)
     f = tb.taylorinteg(tape, q0, 0.0, tmax, 28, 1e-20, mu, maxsteps=2000, kernel_opts={"wide": True}, mode="fast")
     assert np.abs(f.xfinal - ref.xfinal).max() < 1e-9
+
+
+def test_cluster_layout_of_the_shared_memory_kernel():
+    """tb_wide2.cu: many-spin 100 = one coupling cluster per spin (+ its small dq[3i-2] cluster on the same thread),
+    400 stored series (300 state jets + 100 coupling sums) x 26 doubles = 83 KB in shared memory, plus the 100 x 100
+    coupling constants (80 KB, loop-invariant): one CTA per SM."""
+    info = api.WideKernel(P.manyspin_tape(100), 25).info()
+    assert info["threads"] == 128 and info["stored_series"] == 400 and info["scalar_slots"] <= 4
+    assert 160 * 1024 <= info["smem_bytes"] <= 180 * 1024 and info["ctas_per_sm"] == 1
+    k = api.WideKernel(P.kepler_tape(), 28).info()   # one cluster: everything depends on r^3
+    assert k["threads"] == 32 and k["stored_series"] >= 8
+
+
+@pytest.mark.gpu
+def test_gpu_manyspin100_config4_sample_and_kernel_equivalence(monkeypatch):
+    """BASELINE config 4 (100 spins, order 25, tmax 10): 64 members on the shared-memory cluster kernel, a strided
+    sample of them bit for bit against the oracle, all of them against the global-workspace kernel (TB_WIDE_V1)."""
+    tape = P.manyspin_tape(100)
+    q0 = P.manyspin_ensemble(100, 64)
+    sol = tb.taylorinteg(tape, q0, 0.0, 10.0, 25, 1e-20, maxsteps=5000)
+    assert (sol.status == 0).all() and (sol.tfinal == 10.0).all()
+    assert np.abs((sol.xfinal.reshape(100, 3, -1) ** 2).sum(1) - 1.0).max() < 1e-12
+    idx = np.arange(0, 64, 8)
+    ref = oracle.integrate(tape, 25, np.ascontiguousarray(q0[:, idx]), 0.0, 10.0, maxsteps=5000, nthreads=8)
+    assert np.array_equal(sol.nsteps[idx], ref.nsteps) and np.array_equal(sol.xfinal[:, idx], ref.xfinal)
+    monkeypatch.setenv("TB_WIDE_V1", "1")
+    v1 = tb.taylorinteg(tape, q0, 0.0, 10.0, 25, 1e-20, maxsteps=5000)
+    assert np.array_equal(v1.nsteps, sol.nsteps) and np.array_equal(v1.xfinal, sol.xfinal)
+    f = tb.taylorinteg(tape, q0[:, :8], 0.0, 2.0, 25, 1e-20, maxsteps=5000, mode="fast")
+    monkeypatch.delenv("TB_WIDE_V1")
+    f2 = tb.taylorinteg(tape, q0[:, :8], 0.0, 2.0, 25, 1e-20, maxsteps=5000, mode="fast")
+    assert np.abs(f.xfinal - f2.xfinal).max() < 1e-9
