@@ -323,6 +323,17 @@ int tb_jet(tb_kernel_t *k, int64_t N, const double *q0, const double *params, do
 int tb_dense_eval(int64_t N, int32_t dof, int32_t order, int64_t stride, const double *tv,
                   const double *psol, const int64_t *nsteps, const double *tq, int64_t nq, double *xq);
 
+/* the same on DEVICE buffers (psol, tv, nsteps as the ensemble kernel wrote them; nothing is copied) */
+int tb_dense_eval_device(int64_t N, int32_t dof, int32_t order, int64_t stride, const double *d_tv, const double *d_psol,
+                         const int64_t *d_nsteps, const double *d_tq, int64_t nq, double *d_xq, void *stream);
+
+/* psol in the ensemble layout -> the flat vector of `TaylorSolutionSerialization` (src/integrator/taylorsolution.jl:
+ * 513-557): trajectory i occupies d_out[d_offsets[i] ...], element ((c*nsteps[i] + s)*(order+1) + k) = coefficient k of
+ * component c in step s (the order `eachindex(sol.p)` walks the steps x dof matrix, coefficients contiguous).
+ * max_nsteps = max_i nsteps[i].  Device buffers; one bandwidth-bound transposing kernel.                        */
+int tb_serialize_device(int64_t N, int32_t dof, int32_t order, int64_t stride, int64_t max_nsteps, const double *d_psol,
+                        const int64_t *d_nsteps, const int64_t *d_offsets, double *d_out, void *stream);
+
 /* ---- TaylorN jet transport ----------------------------------------------------
  * taylorinteg with U = TaylorN{Float64} (docs/src/pendulum.md:92-108, test/jettransport.jl;
  * solcoeff! src/TaylorIntegration.jl:54-65, _norminf src/integrator/stepsize.jl:26-42):

@@ -18,3 +18,5 @@ __all__ = ["taylorinteg", "lyap_taylorinteg", "taylorize", "TaylorSolution", "En
            "sin", "cos", "sqrt", "exp", "log", "zero", "fp64_peak", "problems", "TaylorB200Error",
            "JetTransport", "JetSolution", "taylorinteg_jet", "sharding", "taylorinteg_sharded",
            "lyap_taylorinteg_sharded"]
+from . import solution  # noqa: F401,E402
+from .solution import DenseEnsemble, flipsign, join, reverse  # noqa: F401,E402

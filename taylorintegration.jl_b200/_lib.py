@@ -87,7 +87,7 @@ class TbOut(C.Structure):
 
 EXPORTS = [
     "tb_abi_version", "tb_last_error", "tb_ode_create", "tb_ode_free", "tb_opts_default", "tb_compile_opts_default",
-    "tb_generate_source", "tb_compile", "tb_integrate_multi", "tb_wide_layout", "tb_kernel_free", "tb_kernel_source", "tb_kernel_log", "tb_kernel_info",
+    "tb_generate_source", "tb_compile", "tb_integrate_multi", "tb_wide_layout", "tb_dense_eval_device", "tb_serialize_device", "tb_kernel_free", "tb_kernel_source", "tb_kernel_log", "tb_kernel_info",
     "tb_kernel_cubin", "tb_integrate", "tb_integrate_trange", "tb_work_bytes", "tb_integrate_device",
     "tb_launch_count", "tb_jet", "tb_dense_eval", "tb_fp64_peak", "tb_device_count", "tb_set_device",
     "tb_tn_create", "tb_tn_free", "tb_tn_ncoef", "tb_tn_monomials", "tb_tn_integrate",
@@ -148,6 +148,8 @@ def lib() -> C.CDLL:
     L.tb_jet.argtypes = [vp, C.c_int64, vp, vp, C.c_double, C.POINTER(TbOpts), vp, vp]
     L.tb_dense_eval.argtypes = [C.c_int64, C.c_int32, C.c_int32, C.c_int64, vp, vp, vp, vp, C.c_int64, vp]
     L.tb_fp64_peak.argtypes = [C.c_double, _DP, _DP]
+    L.tb_dense_eval_device.argtypes = [C.c_int64, C.c_int32, C.c_int32, C.c_int64, vp, vp, vp, vp, C.c_int64, vp, vp]
+    L.tb_serialize_device.argtypes = [C.c_int64, C.c_int32, C.c_int32, C.c_int64, C.c_int64, vp, vp, vp, vp, vp]
     L.tb_set_device.argtypes = [C.c_int]
     L.tb_tn_create.restype = vp
     L.tb_tn_create.argtypes = [vp, C.c_int, C.c_int, C.c_int, C.c_int]

@@ -9,6 +9,7 @@
  */
 #include <cuda_runtime.h>
 
+#include <algorithm>
 #include <cstdint>
 #include <string>
 
@@ -76,16 +77,80 @@ __global__ void dense_eval_kernel(long long N, int dof, int order, long long str
     for (int c = 0; c < dof; c++) {
         double v = nan;
         if (inside) {
-            const double dt = t - tv[s * N + i];
+            const double dt = __dsub_rn(t, tv[s * N + i]);
             const double *p = psol + ((long long)c * np1 * stride + s) * N + i;
+            /* evaluate (Horner) with separate multiply and add like the reference and the parity kernels */
             v = p[(long long)order * stride * N];
-            for (int k = order - 1; k >= 0; k--) v = v * dt + p[(long long)k * stride * N];
+            for (int k = order - 1; k >= 0; k--) v = __dadd_rn(__dmul_rn(v, dt), p[(long long)k * stride * N]);
         }
         xq[((long long)c * nq + q) * N + i] = v;
     }
 }
 
+/* TaylorSolutionSerialization layout (src/integrator/taylorsolution.jl:513-557): per trajectory the flat vector
+ * p[((c*ns + s)*(order+1)) + k], i.e. component-major, then step, coefficients contiguous.  The ensemble kernel writes
+ * psol[((c*(order+1) + k)*stride + s)*N + i] (trajectory fastest).  One warp moves the (order+1) coefficients of 32
+ * trajectories of one (c, s) through shared memory: coalesced reads along i, contiguous writes along k.        */
+__global__ void __launch_bounds__(256) serialize_kernel(long long N, int dof, int order, long long stride, const double *__restrict__ psol,
+                                                        const long long *__restrict__ nsteps, const long long *__restrict__ offs,
+                                                        double *__restrict__ out, long long smax) {
+    extern __shared__ double tile[]; /* [warps][np1][33] */
+    const int np1 = order + 1, lane = threadIdx.x & 31, w = threadIdx.x >> 5, nw = blockDim.x >> 5;
+    double *T = tile + (size_t)w * np1 * 33;
+    const long long i0 = (long long)blockIdx.x * 32;
+    const long long i = i0 + lane;
+    const long long ns_i = i < N ? nsteps[i] : 0;
+    for (long long cs = (long long)blockIdx.y * nw + w; cs < (long long)dof * smax; cs += (long long)gridDim.y * nw) {
+        const int c = (int)(cs / smax);
+        const long long sidx = cs % smax;
+        /* read: lane = trajectory */
+        for (int k = 0; k < np1; k++)
+            T[k * 33 + lane] = (i < N && sidx < ns_i) ? psol[(((long long)c * np1 + k) * stride + sidx) * N + i] : 0.0;
+        __syncwarp();
+        /* write: lane = coefficient */
+        for (int j = 0; j < 32; j++) {
+            const long long tj = i0 + j;
+            if (tj >= N) break;
+            const long long nsj = nsteps[tj];
+            if (sidx >= nsj) continue;
+            double *dst = out + offs[tj] + ((long long)c * nsj + sidx) * np1;
+            for (int k = lane; k < np1; k += 32) dst[k] = T[k * 33 + j];
+        }
+        __syncwarp();
+    }
+}
+
 } // namespace
+
+/* sol(t) on DEVICE buffers: everything stays resident (psol as the ensemble kernel wrote it) */
+extern "C" int tb_dense_eval_device(int64_t N, int32_t dof, int32_t order, int64_t stride, const double *d_tv, const double *d_psol,
+                                    const int64_t *d_nsteps, const double *d_tq, int64_t nq, double *d_xq, void *stream) {
+    if (N <= 0 || nq <= 0) return TB_OK;
+    if (!d_tv || !d_psol || !d_nsteps || !d_tq || !d_xq || nq > 65535) { tb::set_error("tb_dense_eval_device: bad argument"); return TB_ERR_ARG; }
+    dim3 grid((unsigned)((N + 127) / 128), (unsigned)nq);
+    dense_eval_kernel<<<grid, 128, 0, (cudaStream_t)stream>>>(N, dof, order, stride, d_tv, d_psol, (const long long *)d_nsteps, d_tq, nq, d_xq);
+    tb::count_launch(1);
+    TB_CUDA(cudaGetLastError());
+    return TB_OK;
+}
+
+/* psol (device, ensemble layout) -> the reference's serialization layout (device), offsets[i] = first double of trajectory i */
+extern "C" int tb_serialize_device(int64_t N, int32_t dof, int32_t order, int64_t stride, int64_t max_nsteps, const double *d_psol,
+                                   const int64_t *d_nsteps, const int64_t *d_offsets, double *d_out, void *stream) {
+    if (N <= 0 || max_nsteps <= 0) return TB_OK;
+    if (!d_psol || !d_nsteps || !d_offsets || !d_out || dof < 1 || order < 0) { tb::set_error("tb_serialize_device: bad argument"); return TB_ERR_ARG; }
+    const int threads = 256, nw = threads / 32, np1 = order + 1;
+    const size_t smem = (size_t)nw * np1 * 33 * sizeof(double);
+    if (smem > 200 * 1024) { tb::set_error("tb_serialize_device: order too large"); return TB_ERR_UNSUPPORTED; }
+    TB_CUDA(cudaFuncSetAttribute(serialize_kernel, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)smem));
+    const long long work = (long long)dof * max_nsteps;
+    dim3 grid((unsigned)((N + 31) / 32), (unsigned)std::max<long long>(1, std::min<long long>(64, (work + nw - 1) / nw)));
+    serialize_kernel<<<grid, threads, smem, (cudaStream_t)stream>>>(N, dof, order, stride, d_psol, (const long long *)d_nsteps,
+                                                                     (const long long *)d_offsets, d_out, max_nsteps);
+    tb::count_launch(1);
+    TB_CUDA(cudaGetLastError());
+    return TB_OK;
+}
 
 extern "C" int tb_fp64_peak(double seconds, double *tflops, double *ms_out) {
     int dev = 0, n = 0;

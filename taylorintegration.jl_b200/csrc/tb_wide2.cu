@@ -132,15 +132,19 @@ __device__ __forceinline__ void exec2(const W2Args &A, double *__restrict__ W, d
             else if (sa) r = XM(na, rd(o.b, k));
             else if (sb) r = XM(rd(o.a, k), nb);
             else { /* Cauchy product; a negated operand is negated on the fly (exact: a sign bit on the DMUL operand) */
-                const double *a = W + o.a, *b = W + o.b;
-                if (((o.flags & 1) != 0) != ((o.flags & 2) != 0)) {
-                    r = XM(-a[0], b[k * NS]);
-#pragma unroll 4
-                    for (int i = 1; i <= k; i++) r = mad2<FAST>(-a[i * NS], b[(k - i) * NS], r);
+                const double *pa = W + o.a, *pb = W + o.b + k * NS;
+                const bool neg = ((o.flags & 1) != 0) != ((o.flags & 2) != 0);
+                r = XM(neg ? -pa[0] : pa[0], pb[0]);
+                if (FAST) {
+                    for (int i = 1; i <= k; i++) { pa += NS; pb -= NS; r = fma(neg ? -pa[0] : pa[0], pb[0], r); }
                 } else {
-                    r = XM(a[0], b[k * NS]);
-#pragma unroll 4
-                    for (int i = 1; i <= k; i++) r = mad2<FAST>(a[i * NS], b[(k - i) * NS], r);
+                    int i = 1;
+                    for (; i + 2 <= k + 1; i += 2) { /* two products ahead of the dependent adds */
+                        const double q0 = XM(pa[NS], pb[-NS]), q1 = XM(pa[2 * NS], pb[-2 * NS]);
+                        pa += 2 * NS; pb -= 2 * NS;
+                        r = XA(r, neg ? -q0 : q0); r = XA(r, neg ? -q1 : q1);
+                    }
+                    for (; i <= k; i++) { pa += NS; pb -= NS; const double q = XM(pa[0], pb[0]); r = XA(r, neg ? -q : q); }
                 }
             }
             break;
@@ -231,29 +235,38 @@ __device__ __forceinline__ void exec2(const W2Args &A, double *__restrict__ W, d
         }
         case W_LINCOMB: { /* ((start + c1 x1[k]) + c2 x2[k]) + ... : the fused add!/mul! chain, in tape order */
             const double *cf = lcc + o.lc_off;
-            const int *sr = A.lc_ser + o.lc_soff;
             const double *Wk = W + k * NS;
-            const int ls = o.lc_stride, ss = o.lc_sstride, n = o.lc_n;
+            const int ls = o.lc_stride, n = o.lc_n;
             int j = 0;
-            if (sa) { /* numeric start: add!(c, a::Number, b, k) touches k = 0 only */
-                const double m0 = XM(cf[0], Wk[__ldg(sr)]);
-                r = k == 0 ? XA(na, m0) : m0;
-                j = 1;
-            } else r = rd(o.a, k);
-            /* the products of the next terms are formed ahead of the dependent add chain */
-            for (; j + 4 <= n; j += 4) {
-                const double c0 = cf[(size_t)j * ls], c1 = cf[(size_t)(j + 1) * ls];
-                const double c2 = cf[(size_t)(j + 2) * ls], c3 = cf[(size_t)(j + 3) * ls];
-                const double x0 = Wk[__ldg(sr + (size_t)j * ss)], x1 = Wk[__ldg(sr + (size_t)(j + 1) * ss)];
-                const double x2 = Wk[__ldg(sr + (size_t)(j + 2) * ss)], x3 = Wk[__ldg(sr + (size_t)(j + 3) * ss)];
-                if (FAST) { r = fma(c0, x0, r); r = fma(c1, x1, r); r = fma(c2, x2, r); r = fma(c3, x3, r); }
-                else {
-                    const double p0 = XM(c0, x0), p1 = XM(c1, x1), p2 = XM(c2, x2), p3 = XM(c3, x3);
-                    r = XA(r, p0); r = XA(r, p1); r = XA(r, p2); r = XA(r, p3);
+            if (o.lc_sstride == 0) {
+                /* the terms are consecutive stored series (x_1[k], x_2[k], ...: the state jets of the other clusters):
+                 * no id table, the operand pointer just advances; products are formed one batch ahead of the adds */
+                const double *xs = Wk + o.lc_soff;
+                const int xstep = o.pad;
+                if (sa) { const double m0 = XM(__ldg(cf), xs[0]); r = k == 0 ? XA(na, m0) : m0; j = 1; cf += ls; xs += xstep; }
+                else r = rd(o.a, k);
+                if (FAST) {
+                    for (; j < n; j++, cf += ls, xs += xstep) r = fma(__ldg(cf), xs[0], r);
+                } else {
+                    double p0 = 0.0, p1 = 0.0, p2 = 0.0, p3 = 0.0;
+                    bool have = false;
+                    for (; j + 4 <= n; j += 4) {
+                        const double q0 = XM(__ldg(cf), xs[0]), q1 = XM(__ldg(cf + ls), xs[xstep]);
+                        const double q2 = XM(__ldg(cf + 2 * ls), xs[2 * xstep]), q3 = XM(__ldg(cf + 3 * ls), xs[3 * xstep]);
+                        cf += 4 * ls; xs += 4 * xstep;
+                        if (have) { r = XA(r, p0); r = XA(r, p1); r = XA(r, p2); r = XA(r, p3); }
+                        p0 = q0; p1 = q1; p2 = q2; p3 = q3; have = true;
+                    }
+                    if (have) { r = XA(r, p0); r = XA(r, p1); r = XA(r, p2); r = XA(r, p3); }
+                    for (; j < n; j++, cf += ls, xs += xstep) r = XA(r, XM(__ldg(cf), xs[0]));
                 }
+            } else {
+                const int *sr = A.lc_ser + o.lc_soff;
+                const int ss = o.lc_sstride;
+                if (sa) { const double m0 = XM(__ldg(cf), Wk[__ldg(sr)]); r = k == 0 ? XA(na, m0) : m0; j = 1; cf += ls; sr += ss; }
+                else r = rd(o.a, k);
+                for (; j < n; j++, cf += ls, sr += ss) r = mad2<FAST>(__ldg(cf), Wk[__ldg(sr)], r);
             }
-            for (; j < n; j++) r = mad2<FAST>(cf[(size_t)j * ls], Wk[__ldg(sr + (size_t)j * ss)], r);
-            (void)lc_smem;
             break;
         }
         default: break;
@@ -652,12 +665,19 @@ Wide2 *wide2_build(const Program &p, std::string &why) {
             if (o.op == W_LINCOMB) {
                 d.lc_n = o.lc_n; d.lc_off = (int)(cbase + lc_rank[c]); d.lc_stride = nlc;
                 d.lc_soff = (int)(uniform ? sbase : sbase + c); d.lc_sstride = uniform ? 1 : ncl;
+                d.pad = 0;
                 for (int t = 0; t < o.lc_n; t++) {
                     int ng;
                     const int l = loc(p.lc_ser[o.lc_off + t], &ng);
                     if (l < 0 || ng) bad = "a linear-combination term is not a stored series"; /* terms are state jets in practice */
                     w->lc_coef[cbase + (size_t)t * nlc + lc_rank[c]] = p.lc_coef[o.lc_off + t];
                     w->lc_ser[uniform ? sbase + t : sbase + (size_t)t * ncl + c] = l;
+                }
+                if (uniform && o.lc_n >= 2) { /* consecutive stored series? then the kernel walks a pointer */
+                    const int s0 = w->lc_ser[sbase], ds = w->lc_ser[sbase + 1] - s0;
+                    bool affine = true;
+                    for (int t = 2; t < o.lc_n && affine; t++) affine = w->lc_ser[sbase + t] == s0 + t * ds;
+                    if (affine) { d.lc_sstride = 0; d.lc_soff = s0; d.pad = ds; }
                 }
             }
         }
@@ -671,7 +691,9 @@ Wide2 *wide2_build(const Program &p, std::string &why) {
      * they are copied to shared memory once per CTA when they fit beside the jets.  From global memory the dependent
      * add chain waits on L2 (measured on many-spin 100: 9.1e5 steps/s with 2 CTAs per SM and the table in L1/L2).  */
     w->lc_smem = !w->lc_coef.empty() && w->smem + w->lc_coef.size() * sizeof(double) + 1024 <= smem_max;
-    if (getenv("TB_WIDE_LC_GLOBAL")) w->lc_smem = false;
+    /* measured: 6.4e5 steps/s with the table in shared memory (1 CTA per SM) against 9.3e5 from L1/L2 with 2 CTAs per
+     * SM: occupancy wins, so the table stays in global memory unless TB_WIDE_LC_SMEM=1 asks otherwise */
+    if (!getenv("TB_WIDE_LC_SMEM")) w->lc_smem = false;
     if (w->lc_smem) w->smem += w->lc_coef.size() * sizeof(double);
     if (w->smem > smem_max) { why = "stored series do not fit shared memory (" + std::to_string(w->smem) + " B)"; delete w; return nullptr; }
     w->ctas = (int)std::max<size_t>(1, std::min<size_t>(smem_max / (w->smem + 1024), 2048 / threads));

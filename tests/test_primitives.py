@@ -79,6 +79,10 @@ def test_gpu_matches_oracle_bitwise():
         for i in range(0, 70, 5):
             xo, _, dto = oracle.jet(tape, order, q0[:, i], par, t0=0.1)
             assert np.array_equal(xj[:, :, i], xo) and dt[i] == dto
-    g = tb.taylorinteg(tape, q0, 0.1, 3.0, 17, 1e-18, par, maxsteps=2000)
+    import warnings
+    with warnings.catch_warnings():
+        warnings.simplefilter("ignore")  # some members run into the branch point of asin (zero step): same on both sides
+        g = tb.taylorinteg(tape, q0, 0.1, 3.0, 17, 1e-18, par, maxsteps=2000)
     o = oracle.integrate(tape, 17, q0, 0.1, 3.0, par, abstol=1e-18, maxsteps=2000)
-    assert np.array_equal(g.xfinal, o.xfinal) and np.array_equal(g.nsteps, o.nsteps) and not g.status.any()
+    assert np.array_equal(g.xfinal, o.xfinal) and np.array_equal(g.nsteps, o.nsteps) and np.array_equal(g.status, o.status)
+    assert (g.status == 0).sum() >= 5 and np.array_equal(g.tfinal, o.tfinal)
