@@ -369,9 +369,10 @@ void tb_wide_free(tb_wide_t *w);
 int tb_wide_info(const tb_wide_t *w, int *nops, int *nlev, int *nser, int *maxwidth);
 /* the shared-memory cluster kernel (jets [order][series] in shared memory, one thread per cluster of same-order
  * dependent entries, one barrier per order): clusters, stored series, scalar slots, CTA size, shared memory per CTA,
- * CTAs per SM.  TB_ERR_UNSUPPORTED when the stored series do not fit (the global-workspace kernel runs then).      */
+ * CTAs per SM, and the number of groups of isomorphic clusters that share ONE copy of their entries (0: every cluster
+ * carries its own).  TB_ERR_UNSUPPORTED when the stored series do not fit (the global-workspace kernel runs then). */
 int tb_wide_layout(const tb_wide_t *w, int *nclusters, int *npersistent, int *ntransient, int *threads, int *smem_bytes,
-                   int *ctas_per_sm);
+                   int *ctas_per_sm, int *ngroups);
 int tb_wide_integrate(tb_wide_t *w, int64_t N, const double *q0, const double *params, double t0, double tmax,
                       const double *trange, int64_t nt, const tb_opts_t *opts, const tb_out_t *out);
 

@@ -163,7 +163,7 @@ def lib() -> C.CDLL:
     L.tb_wide_create.argtypes = [vp, C.c_int, C.c_int]
     L.tb_wide_free.argtypes = [vp]
     L.tb_wide_info.argtypes = [vp] + [C.POINTER(C.c_int)] * 4
-    L.tb_wide_layout.argtypes = [vp] + [C.POINTER(C.c_int)] * 6
+    L.tb_wide_layout.argtypes = [vp] + [C.POINTER(C.c_int)] * 7
     L.tb_wide_integrate.argtypes = [vp, C.c_int64, vp, vp, C.c_double, C.c_double, vp, C.c_int64, C.POINTER(TbOpts),
                                     C.POINTER(TbOut)]
     _lib = L

@@ -135,9 +135,9 @@ class WideKernel:
         v = [C.c_int(-1) for _ in range(4)]
         L.lib().tb_wide_info(self._w, *[C.byref(x) for x in v])
         d = dict(zip(["entries", "levels", "series", "max_width"], [x.value for x in v]))
-        v2 = [C.c_int(-1) for _ in range(6)]
+        v2 = [C.c_int(-1) for _ in range(7)]
         if L.lib().tb_wide_layout(self._w, *[C.byref(x) for x in v2]) == 0:  # the shared-memory cluster kernel applies
-            d.update(zip(["clusters", "stored_series", "scalar_slots", "threads", "smem_bytes", "ctas_per_sm"],
+            d.update(zip(["clusters", "stored_series", "scalar_slots", "threads", "smem_bytes", "ctas_per_sm", "groups"],
                          [x.value for x in v2]))
         return d
 

@@ -543,10 +543,11 @@ int tb_wide_info(const tb_wide_t *w, int *nops, int *nlev, int *nser, int *maxwi
 }
 
 /* layout of the shared-memory cluster kernel; TB_ERR_UNSUPPORTED (reason in tb_last_error) when it does not apply */
-int tb_wide_layout(const tb_wide_t *w, int *nclusters, int *npersistent, int *ntransient, int *threads, int *smem_bytes, int *ctas_per_sm) {
+int tb_wide_layout(const tb_wide_t *w, int *nclusters, int *npersistent, int *ntransient, int *threads, int *smem_bytes, int *ctas_per_sm,
+                   int *ngroups) {
     if (!w) return TB_ERR_ARG;
     if (!w->v2) { tb::set_error("tb_wide_layout: " + w->v2_why); return TB_ERR_UNSUPPORTED; }
-    tbw::wide2_info(w->v2, nclusters, npersistent, ntransient, threads, smem_bytes, ctas_per_sm);
+    tbw::wide2_info(w->v2, nclusters, npersistent, ntransient, threads, smem_bytes, ctas_per_sm, ngroups);
     return TB_OK;
 }
 

@@ -17,6 +17,8 @@
  *     Every other series is a scalar of the current order in a [slot][thread] scratch.  A negated series that only
  *     feeds Cauchy products is not stored: the product negates its operand (exact).  Many-spin 100: 400 series x 26
  *     doubles = 83 KB per CTA, two CTAs per SM.
+ *   - GROUP PROGRAMS.  Isomorphic clusters share ONE copy of their entries (operands shift by the cluster's rank),
+ *     held in shared memory with the per-cluster literals: every lane reads the same entry (broadcast).
  *   - coupling constants come from global memory term-major ([term][cluster]: coalesced, L1/L2 resident).
  * Bound: FP64 pipe; the coupling sum is one dependent DADD chain per thread (parity order).
  */
@@ -24,7 +26,9 @@
 
 #include <algorithm>
 #include <cstdint>
+#include <cstdio>
 #include <cstdlib>
+#include <cstring>
 #include <map>
 #include <numeric>
 #include <string>
@@ -69,6 +73,11 @@ struct W2Args {
     const int *xsid; /* [dof] persistent id of x[c] */
     const int *cl_len; /* [ncl] entries of cluster c (0: a padding slot) */
     int lc_smem, lc_count; /* coupling constants copied to shared memory (lc_count doubles) */
+    int ngroups;           /* > 0: group programs */
+    int g_smem, ngops, ngnum; /* group programs copied to shared memory */
+    int g_first[8], g_count[8], g_off[8], g_len[8];
+    const C2Op *gops;
+    const double *gnum;
     const double *q0, *params, *trange;
     long long nt;
     double t0, tmax, abstol, reltol, minstep, maxstep;
@@ -243,29 +252,29 @@ __device__ __forceinline__ void exec2(const W2Args &A, double *__restrict__ W, d
                  * no id table, the operand pointer just advances; products are formed one batch ahead of the adds */
                 const double *xs = Wk + o.lc_soff;
                 const int xstep = o.pad;
-                if (sa) { const double m0 = XM(__ldg(cf), xs[0]); r = k == 0 ? XA(na, m0) : m0; j = 1; cf += ls; xs += xstep; }
+                if (sa) { const double m0 = XM(cf[0], xs[0]); r = k == 0 ? XA(na, m0) : m0; j = 1; cf += ls; xs += xstep; }
                 else r = rd(o.a, k);
                 if (FAST) {
-                    for (; j < n; j++, cf += ls, xs += xstep) r = fma(__ldg(cf), xs[0], r);
+                    for (; j < n; j++, cf += ls, xs += xstep) r = fma(cf[0], xs[0], r);
                 } else {
                     double p0 = 0.0, p1 = 0.0, p2 = 0.0, p3 = 0.0;
                     bool have = false;
                     for (; j + 4 <= n; j += 4) {
-                        const double q0 = XM(__ldg(cf), xs[0]), q1 = XM(__ldg(cf + ls), xs[xstep]);
-                        const double q2 = XM(__ldg(cf + 2 * ls), xs[2 * xstep]), q3 = XM(__ldg(cf + 3 * ls), xs[3 * xstep]);
+                        const double q0 = XM(cf[0], xs[0]), q1 = XM(cf[ls], xs[xstep]);
+                        const double q2 = XM(cf[2 * ls], xs[2 * xstep]), q3 = XM(cf[3 * ls], xs[3 * xstep]);
                         cf += 4 * ls; xs += 4 * xstep;
                         if (have) { r = XA(r, p0); r = XA(r, p1); r = XA(r, p2); r = XA(r, p3); }
                         p0 = q0; p1 = q1; p2 = q2; p3 = q3; have = true;
                     }
                     if (have) { r = XA(r, p0); r = XA(r, p1); r = XA(r, p2); r = XA(r, p3); }
-                    for (; j < n; j++, cf += ls, xs += xstep) r = XA(r, XM(__ldg(cf), xs[0]));
+                    for (; j < n; j++, cf += ls, xs += xstep) r = XA(r, XM(cf[0], xs[0]));
                 }
             } else {
                 const int *sr = A.lc_ser + o.lc_soff;
                 const int ss = o.lc_sstride;
-                if (sa) { const double m0 = XM(__ldg(cf), Wk[__ldg(sr)]); r = k == 0 ? XA(na, m0) : m0; j = 1; cf += ls; sr += ss; }
+                if (sa) { const double m0 = XM(cf[0], Wk[__ldg(sr)]); r = k == 0 ? XA(na, m0) : m0; j = 1; cf += ls; sr += ss; }
                 else r = rd(o.a, k);
-                for (; j < n; j++, cf += ls, sr += ss) r = mad2<FAST>(__ldg(cf), Wk[__ldg(sr)], r);
+                for (; j < n; j++, cf += ls, sr += ss) r = mad2<FAST>(cf[0], Wk[__ldg(sr)], r);
             }
             break;
         }
@@ -306,12 +315,24 @@ template <bool FAST> __global__ void __launch_bounds__(256, 1) wide2_kernel(cons
     double *tr = W + (size_t)(P + 1) * NS + tid;  /* [ntr][nth] transient scalars of the current order */
     double *xnew = W + (size_t)(P + 1) * NS + (size_t)a.ntr * nth; /* [dof] */
     const double *lcc = a.lc_coef;
+    double *extra = xnew + a.dof + 8;
     if (a.lc_smem) { /* loop-invariant coupling constants: once per CTA */
-        double *t = xnew + a.dof + 8;
-        for (int j = tid; j < a.lc_count; j += nth) t[j] = a.lc_coef[j];
-        lcc = t;
-        __syncthreads();
+        for (int j = tid; j < a.lc_count; j += nth) extra[j] = a.lc_coef[j];
+        lcc = extra;
+        extra += a.lc_count;
     }
+    const C2Op *gops = a.gops;
+    const double *gnum = a.gnum;
+    if (a.g_smem) {
+        double *gn = extra;
+        for (int j = tid; j < a.ngnum; j += nth) gn[j] = a.gnum[j];
+        int *go = (int *)(gn + a.ngnum);
+        const int *src = (const int *)a.gops;
+        for (int j = tid; j < a.ngops * (int)(sizeof(C2Op) / 4); j += nth) go[j] = src[j];
+        gnum = gn;
+        gops = (const C2Op *)go;
+    }
+    __syncthreads();
     const double inf = __longlong_as_double(0x7FF0000000000000LL), nan = __longlong_as_double(0x7FF8000000000000LL);
     for (;;) {
         if (tid == 0) s_idx = atomicAdd(a.counter, 1ull);
@@ -340,6 +361,24 @@ template <bool FAST> __global__ void __launch_bounds__(256, 1) wide2_kernel(cons
             __syncthreads();
             /* jetcoeffs!: for ord = 0:order-1 (parse_eqs.jl:259-264); every cluster in tape order, then ONE barrier */
             for (int k = 0; k < P; k++) {
+                if (a.ngroups > 0) {
+                    for (int g = 0; g < a.ngroups; g++)
+                        for (int r = tid; r < a.g_count[g]; r += nth)
+                            for (int j = 0; j < a.g_len[g]; j++) {
+                                C2Op o = gops[a.g_off[g] + j]; /* the same entry for every lane: a broadcast from shared memory */
+                                long long no;
+                                memcpy(&no, &o.immb, sizeof no);
+                                const double lit = ((o.a == -1 && o.para < 0) || (o.b == -1 && o.parb < 0)) ? gnum[no + r] : 0.0;
+                                o.imma = lit; o.immb = lit;
+                                if (o.flags & 16) o.res += r;
+                                if (o.flags & 32) o.a += r;
+                                if (o.flags & 64) o.b += r;
+                                if (o.flags & 128) o.aux += r;
+                                o.lc_off += r;
+                                if (o.flags & 256) o.lc_soff += r;
+                                exec2<FAST>(a, W, tr, par, lcc, a.lc_smem != 0, o, k);
+                            }
+                } else
                 for (int c = tid; c < a.ncl; c += nth) {
                     const int len = __ldg(a.cl_len + c);
                     for (int j = 0; j < len; j++) exec2<FAST>(a, W, tr, par, lcc, a.lc_smem != 0, a.ops[(size_t)j * a.ncl + c], k);
@@ -433,10 +472,15 @@ template <bool FAST> __global__ void __launch_bounds__(256, 1) wide2_kernel(cons
 struct Wide2 {
     int order = 0, mode = 0, dof = 0, npar = 0, NS = 0, ncl = 0, maxlen = 0, ntr = 0, tsid = -1, threads = 0, ctas = 1;
     size_t smem = 0;
-    bool lc_smem = false;
+    bool lc_smem = false, g_smem = false;
     std::vector<C2Op> ops;
     std::vector<double> lc_coef;
     std::vector<int> lc_ser, xsid, cl_len;
+    std::vector<C2Op> gops;      /* group programs (empty: per-cluster entries) */
+    std::vector<double> gnum;    /* literal of entry j for cluster rank r */
+    std::vector<int> g_first, g_count, g_off, g_len;
+    C2Op *d_gops = nullptr;
+    double *d_gnum = nullptr;
     int device = -1;
     C2Op *d_ops = nullptr;
     double *d_lcc = nullptr;
@@ -532,6 +576,7 @@ Wide2 *wide2_build(const Program &p, std::string &why) {
     }
     int ncl = (int)cl_ops.size();
     int threads_pick = 32;
+    std::vector<int> grp_first, grp_count; /* isomorphic clusters, contiguous in the layout */
     if (ncl == 0) { why = "empty program"; return nullptr; }
     /* solcoeff! of component c runs in the cluster that produces dx[c] */
     std::vector<std::vector<int>> cl_sol(ncl);
@@ -570,6 +615,8 @@ Wide2 *wide2_build(const Program &p, std::string &why) {
         std::vector<std::vector<int>> new_ops, new_sol;
         for (auto &og : order) {
             const std::vector<int> &mem = groups[og.second];
+            grp_first.push_back((int)new_ops.size());
+            grp_count.push_back((int)mem.size());
             for (int c : mem) { new_ops.push_back(cl_ops[c]); new_sol.push_back(cl_sol[c]); }
             if (&og != &order.back())
                 while (new_ops.size() % (size_t)threads_pick) { new_ops.emplace_back(); new_sol.emplace_back(); }
@@ -673,16 +720,73 @@ Wide2 *wide2_build(const Program &p, std::string &why) {
                     w->lc_coef[cbase + (size_t)t * nlc + lc_rank[c]] = p.lc_coef[o.lc_off + t];
                     w->lc_ser[uniform ? sbase + t : sbase + (size_t)t * ncl + c] = l;
                 }
-                if (uniform && o.lc_n >= 2) { /* consecutive stored series? then the kernel walks a pointer */
-                    const int s0 = w->lc_ser[sbase], ds = w->lc_ser[sbase + 1] - s0;
+                {   /* equally spaced stored series (or a single term)? then the kernel walks a pointer, no id table */
+                    auto sid_at = [&](int t) { return w->lc_ser[uniform ? sbase + t : sbase + (size_t)t * ncl + c]; };
+                    const int s0 = sid_at(0), ds = o.lc_n >= 2 ? sid_at(1) - s0 : 0;
                     bool affine = true;
-                    for (int t = 2; t < o.lc_n && affine; t++) affine = w->lc_ser[sbase + t] == s0 + t * ds;
+                    for (int t = 2; t < o.lc_n && affine; t++) affine = sid_at(t) == s0 + t * ds;
                     if (affine) { d.lc_sstride = 0; d.lc_soff = s0; d.pad = ds; }
                 }
             }
         }
     }
     if (!bad.empty()) { why = bad; delete w; return nullptr; }
+    /* GROUP PROGRAMS.  The clusters of a group run the same entries; with the role-major numbering their stored
+     * operands differ by the cluster's rank in the group (or not at all), their linear-combination columns by the
+     * rank, and their literal by a per-cluster table.  Then ONE copy of the entries serves the whole group: every
+     * lane of a warp reads the same 80 bytes (a broadcast that stays in L1) instead of its own copy from L2 --
+     * the per-cluster copies are 182 KB for many-spin 100 and their fetch latency was half of the step time.    */
+    {
+        bool ok = grp_count.size() <= 8;
+        std::vector<C2Op> gops;
+        std::vector<double> gnum;
+        std::vector<int> goff, glen;
+        for (size_t g = 0; g < grp_count.size() && ok; g++) {
+            const int c0 = grp_first[g], cnt = grp_count[g], len = w->cl_len[c0];
+            goff.push_back((int)gops.size());
+            glen.push_back(len);
+            for (int j = 0; j < len && ok; j++) {
+                C2Op u = w->ops[(size_t)j * ncl + c0];
+                int dflags = 0;
+                const int num_off = (int)gnum.size();
+                const bool sa = u.a == -1 && u.para < 0, sb = u.b == -1 && u.parb < 0;
+                for (int r = 0; r < cnt && ok; r++) {
+                    const C2Op &v = w->ops[(size_t)j * ncl + c0 + r];
+                    auto delta = [&](int lu, int lv, int bit) {
+                        if (lu < 0) { if (lv != lu) ok = false; return; }
+                        const int dlt = lv - lu;
+                        if (r == 1) { if (dlt == 1) dflags |= bit; else if (dlt != 0) ok = false; }
+                        else if (dlt != ((dflags & bit) ? r : 0)) ok = false;
+                    };
+                    if (getenv("TB_WIDE_DEBUG") && r == 1) fprintf(stderr, "g%zu j%d op %d/%d fl %d/%d par %d/%d %d/%d n %d/%d ls %d/%d ss %d/%d pad %d/%d res %d/%d a %d/%d b %d/%d aux %d/%d off %d/%d soff %d/%d\n", g, j, u.op, v.op, u.flags, v.flags, u.para, v.para, u.parb, v.parb, u.lc_n, v.lc_n, u.lc_stride, v.lc_stride, u.lc_sstride, v.lc_sstride, u.pad, v.pad, u.res, v.res, u.a, v.a, u.b, v.b, u.aux, v.aux, u.lc_off, v.lc_off, u.lc_soff, v.lc_soff);
+                    if (v.op != u.op || v.flags != u.flags || v.para != u.para || v.parb != u.parb || (u.op == TB_OP_POW && v.imm != u.imm) || v.lc_n != u.lc_n ||
+                        v.lc_stride != u.lc_stride || v.lc_sstride != u.lc_sstride || v.pad != u.pad) { ok = false; break; }
+                    delta(u.res, v.res, 16); delta(u.a, v.a, 32); delta(u.b, v.b, 64); delta(u.aux, v.aux, 128);
+                    if (u.op == W_LINCOMB) {
+                        if (v.lc_off != u.lc_off + r) ok = false;
+                        if (u.lc_sstride == 0) delta(u.lc_soff, v.lc_soff, 256);          /* first operand series: fixed or by rank */
+                        else if (u.lc_sstride == 1) { if (v.lc_soff != u.lc_soff) ok = false; } /* shared id table */
+                        else ok = false;                                                  /* per-cluster id tables: keep per-cluster entries */
+                    }
+                    if (!ok && getenv("TB_WIDE_DEBUG")) fprintf(stderr, "FAIL g%zu j%d r%d: res %d/%d a %d/%d b %d/%d aux %d/%d dflags %d off %d/%d soff %d/%d\n", g, j, r, u.res, v.res, u.a, v.a, u.b, v.b, u.aux, v.aux, dflags, u.lc_off, v.lc_off, u.lc_soff, v.lc_soff);
+                    gnum.push_back(sa ? v.imma : (sb ? v.immb : 0.0));
+                }
+                if (cnt == 1) dflags = 0;
+                u.flags |= dflags;
+                u.lc_soff = u.lc_soff;
+                u.pad = u.pad;
+                /* literal of cluster r at gnum[num_off + r]; stash the offset in the (unused here) immb slot as bits */
+                long long no = num_off;
+                memcpy(&u.immb, &no, sizeof no);
+                gops.push_back(u);
+            }
+        }
+        if (ok && !getenv("TB_WIDE_NO_GROUPS")) {
+            w->gops.swap(gops); w->gnum.swap(gnum);
+            for (size_t g = 0; g < grp_count.size(); g++) { w->g_first.push_back(grp_first[g]); w->g_count.push_back(grp_count[g]); }
+            w->g_off = goff; w->g_len = glen;
+        }
+    }
     const int threads = threads_pick;
     w->threads = threads;
     w->smem = ((size_t)(p.order + 1) * NS + (size_t)w->ntr * threads + p.dof + 16) * sizeof(double);
@@ -691,10 +795,14 @@ Wide2 *wide2_build(const Program &p, std::string &why) {
      * they are copied to shared memory once per CTA when they fit beside the jets.  From global memory the dependent
      * add chain waits on L2 (measured on many-spin 100: 9.1e5 steps/s with 2 CTAs per SM and the table in L1/L2).  */
     w->lc_smem = !w->lc_coef.empty() && w->smem + w->lc_coef.size() * sizeof(double) + 1024 <= smem_max;
-    /* measured: 6.4e5 steps/s with the table in shared memory (1 CTA per SM) against 9.3e5 from L1/L2 with 2 CTAs per
-     * SM: occupancy wins, so the table stays in global memory unless TB_WIDE_LC_SMEM=1 asks otherwise */
-    if (!getenv("TB_WIDE_LC_SMEM")) w->lc_smem = false;
+    /* ncu (profiles/r02_ncu_wide2_summary.txt): with the table in L1/L2 the multiplies of the coupling sum wait ~300
+     * cycles per batch of loads, 25 batches per order; TB_WIDE_LC_GLOBAL=1 keeps it in global memory (2 CTAs per SM) */
+    if (!getenv("TB_WIDE_LC_SMEM")) w->lc_smem = false; /* measured (many-spin 100, 2^14 members): 1.17e6 steps/s with the table in
+                                                          * shared memory and 1 CTA per SM, 1.75e6 from L1/L2 with 2 CTAs per SM */
     if (w->lc_smem) w->smem += w->lc_coef.size() * sizeof(double);
+    /* group programs and their literals live in shared memory as well (a few KB) */
+    w->g_smem = !w->gops.empty() && w->smem + w->gops.size() * sizeof(C2Op) + w->gnum.size() * sizeof(double) + 1024 <= smem_max;
+    if (w->g_smem) w->smem += w->gops.size() * sizeof(C2Op) + w->gnum.size() * sizeof(double);
     if (w->smem > smem_max) { why = "stored series do not fit shared memory (" + std::to_string(w->smem) + " B)"; delete w; return nullptr; }
     w->ctas = (int)std::max<size_t>(1, std::min<size_t>(smem_max / (w->smem + 1024), 2048 / threads));
     return w;
@@ -702,11 +810,11 @@ Wide2 *wide2_build(const Program &p, std::string &why) {
 
 void wide2_free(Wide2 *w) {
     if (!w) return;
-    if (w->d_ops) { cudaFree(w->d_ops); cudaFree(w->d_lcc); cudaFree(w->d_lcs); cudaFree(w->d_xs); cudaFree(w->d_len); }
+    if (w->d_ops) { cudaFree(w->d_ops); cudaFree(w->d_lcc); cudaFree(w->d_lcs); cudaFree(w->d_xs); cudaFree(w->d_len); cudaFree(w->d_gops); cudaFree(w->d_gnum); }
     delete w;
 }
 
-void wide2_info(const Wide2 *w, int *nclusters, int *npersist, int *ntransient, int *threads, int *smem_bytes, int *ctas_per_sm) {
+void wide2_info(const Wide2 *w, int *nclusters, int *npersist, int *ntransient, int *threads, int *smem_bytes, int *ctas_per_sm, int *ngroups) {
     if (!w) return;
     if (nclusters) *nclusters = w->ncl;
     if (npersist) *npersist = w->NS;
@@ -714,6 +822,7 @@ void wide2_info(const Wide2 *w, int *nclusters, int *npersist, int *ntransient, 
     if (threads) *threads = w->threads;
     if (smem_bytes) *smem_bytes = (int)w->smem;
     if (ctas_per_sm) *ctas_per_sm = w->ctas;
+    if (ngroups) *ngroups = w->gops.empty() ? 0 : (int)w->g_count.size();
 }
 
 int wide2_integrate(Wide2 *w, long long N, const double *q0, const double *params, double t0, double tmax,
@@ -724,7 +833,7 @@ int wide2_integrate(Wide2 *w, long long N, const double *q0, const double *param
     const int dof = w->dof;
     const bool fast = w->mode == TB_MODE_FAST;
     if (!w->d_ops || w->device != dev) {
-        if (w->d_ops) { cudaFree(w->d_ops); cudaFree(w->d_lcc); cudaFree(w->d_lcs); cudaFree(w->d_xs); cudaFree(w->d_len); w->d_ops = nullptr; }
+        if (w->d_ops) { cudaFree(w->d_ops); cudaFree(w->d_lcc); cudaFree(w->d_lcs); cudaFree(w->d_xs); cudaFree(w->d_len); cudaFree(w->d_gops); cudaFree(w->d_gnum); w->d_ops = nullptr; }
         w->device = dev;
         auto up = [&](void **dst, const void *src, size_t bytes) -> cudaError_t {
             cudaError_t e = cudaMalloc(dst, bytes ? bytes : 8);
@@ -736,6 +845,8 @@ int wide2_integrate(Wide2 *w, long long N, const double *q0, const double *param
         TB_CUDA2(up((void **)&w->d_lcs, w->lc_ser.data(), sizeof(int) * w->lc_ser.size()));
         TB_CUDA2(up((void **)&w->d_xs, w->xsid.data(), sizeof(int) * dof));
         TB_CUDA2(up((void **)&w->d_len, w->cl_len.data(), sizeof(int) * w->cl_len.size()));
+        TB_CUDA2(up((void **)&w->d_gops, w->gops.data(), sizeof(C2Op) * w->gops.size()));
+        TB_CUDA2(up((void **)&w->d_gnum, w->gnum.data(), sizeof(double) * w->gnum.size()));
         if (fast) TB_CUDA2(cudaFuncSetAttribute(wide2_kernel<true>, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)w->smem));
         else TB_CUDA2(cudaFuncSetAttribute(wide2_kernel<false>, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)w->smem));
     }
@@ -747,6 +858,9 @@ int wide2_integrate(Wide2 *w, long long N, const double *q0, const double *param
     W2Args a{};
     a.N = N; a.dof = dof; a.npar = w->npar; a.P = w->order; a.NS = w->NS; a.ncl = w->ncl; a.maxlen = w->maxlen; a.ntr = w->ntr; a.tsid = w->tsid;
     a.ops = w->d_ops; a.lc_coef = w->d_lcc; a.lc_ser = w->d_lcs; a.xsid = w->d_xs; a.cl_len = w->d_len; a.lc_smem = w->lc_smem ? 1 : 0; a.lc_count = (int)w->lc_coef.size();
+    a.ngroups = w->gops.empty() ? 0 : (int)w->g_count.size(); a.gops = w->d_gops; a.gnum = w->d_gnum;
+    a.g_smem = w->g_smem ? 1 : 0; a.ngops = (int)w->gops.size(); a.ngnum = (int)w->gnum.size();
+    for (int g = 0; g < a.ngroups; g++) { a.g_first[g] = w->g_first[g]; a.g_count[g] = w->g_count[g]; a.g_off[g] = w->g_off[g]; a.g_len[g] = w->g_len[g]; }
     a.nt = trange ? nt : 0; a.t0 = t0; a.tmax = tmax; a.abstol = o->abstol; a.reltol = o->reltol; a.minstep = o->minstepsize;
     a.maxstep = o->maxstepsize; a.maxsteps = o->maxsteps; a.params_per_traj = o->params_per_traj;
     const size_t nq = (size_t)dof * N, npar = (size_t)(w->npar > 0 ? w->npar : 1) * (o->params_per_traj ? N : 1);

@@ -152,3 +152,24 @@ def test_gpu_fast_mode_close_to_parity():
     assert np.array_equal(sa.nsteps, sb.nsteps)
     scale = np.abs(sa.xfinal).max()
     assert np.abs(sa.xfinal - sb.xfinal).max() <= 1e-11 * scale
+
+
+@pytest.mark.gpu
+def test_gpu_kepler_4vars_order8_config5b_bitwise():
+    """BASELINE config 5b at its stated shape: kepler1! in 4 variables of order 8 (495 coefficients per component),
+    time order 28; three nominal orbits over a quarter period, bit for bit against the oracle.  The constant term of
+    the jet is the scalar orbit, and the jet evaluated at a displacement matches the displaced integration."""
+    tape = P.kepler_tape()
+    jt = tb.JetTransport(tape, 28, 4, 8)
+    assert jt.ncoef == 495
+    q, mu, _ = P.kepler_ensemble(5)
+    q = np.ascontiguousarray(q[:, [0, 2, 4]])          # e = 0, 0.45, 0.9
+    q0 = jt.initial(q)
+    tmax = np.pi / 2
+    sol = jt.integrate(q0, 0.0, tmax, 1e-20, mu, maxsteps=2000)
+    ref = oracle.integrate_tn(tape, 28, 4, 8, q0, 0.0, tmax, params=mu, maxsteps=2000, abstol=1e-20)
+    assert np.array_equal(sol.nsteps, ref["nsteps"]) and (sol.status == 0).all() and np.all(sol.tfinal == tmax)
+    assert np.array_equal(sol.xfinal, ref["xfinal"])
+    xi = np.array([1e-3, -2e-3, 1.5e-3, -0.5e-3])
+    disp = tb.taylorinteg(tape, q + xi[:, None], 0.0, tmax, 28, 1e-20, mu, maxsteps=2000)
+    assert np.allclose(sol.evaluate(xi)[:, :2], disp.xfinal[:, :2], rtol=0, atol=1e-10)  # e = 0.9 needs |xi| smaller

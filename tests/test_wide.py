@@ -85,11 +85,11 @@ def test_gpu_wide_interpreter_matches_thread_kernel():
 
 def test_cluster_layout_of_the_shared_memory_kernel():
     """tb_wide2.cu: many-spin 100 = one coupling cluster per spin (+ its small dq[3i-2] cluster on the same thread),
-    400 stored series (300 state jets + 100 coupling sums) x 26 doubles = 83 KB in shared memory, plus the 100 x 100
-    coupling constants (80 KB, loop-invariant): one CTA per SM."""
+    400 stored series (300 state jets + 100 coupling sums) x 26 doubles = 83 KB in shared memory, two CTAs per SM (the
+    100 x 100 coupling constants stay in L1/L2: measured faster than 1 CTA per SM with them in shared memory); the two kinds of cluster (coupling, dq[3i-2]) each share one copy of their entries (group programs)."""
     info = api.WideKernel(P.manyspin_tape(100), 25).info()
     assert info["threads"] == 128 and info["stored_series"] == 400 and info["scalar_slots"] <= 4
-    assert 160 * 1024 <= info["smem_bytes"] <= 180 * 1024 and info["ctas_per_sm"] == 1
+    assert info["smem_bytes"] <= 110 * 1024 and info["ctas_per_sm"] == 2 and info["groups"] == 2
     k = api.WideKernel(P.kepler_tape(), 28).info()   # one cluster: everything depends on r^3
     assert k["threads"] == 32 and k["stored_series"] >= 8
 
