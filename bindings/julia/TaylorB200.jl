@@ -12,7 +12,7 @@
 #     end
 module TaylorB200
 
-export taylorize, taylorinteg, Tape
+export taylorize, taylorinteg, taylorinteg_events, taylorinteg_trange, free_kernels, Tape
 
 const LIB = get(ENV, "TAYLORB200_LIB", "libtaylorb200.so")
 
@@ -31,7 +31,7 @@ struct TbOdeDesc
 end
 mutable struct TbCompileOpts
     order::Int32; mode::Int32; kind::Int32; block_threads::Int32
-    reg_budget::Int32; min_blocks_per_sm::Int32; flags::Int32; reserved::Int32
+    reg_budget::Int32; min_blocks_per_sm::Int32; flags::Int32; tmem_budget::Int32
     TbCompileOpts() = new(0, 0, 0, 0, 0, 0, 0, 0)
 end
 mutable struct TbOpts
@@ -53,7 +53,7 @@ mutable struct TbOut
 end
 
 const OP = (IDENTITY = 1, NEG = 2, ADD = 3, SUB = 4, MUL = 5, DIV = 6, SQR = 7, SQRT = 8, POW = 9, EXP = 10,
-            LOG = 11, SINCOS = 12)
+            LOG = 11, SINCOS = 12, TAN = 15, SINHCOSH = 16, TANH = 17, ATAN = 18, ASIN = 19, ACOS = 20)
 const K_NONE, K_X, K_DX, K_TMP, K_PAR, K_TIME, K_IMM = 0, 1, 2, 3, 4, 5, 6
 operand(kind, index) = Int32((UInt32(kind) << 24) | (UInt32(index) & 0x00ffffff))
 const ST_MAXSTEPS, ST_ZERO_STEP, ST_NR_NOCONV = 1, 2, 4
@@ -108,19 +108,44 @@ function taylorize(f!, dof::Integer, npar::Integer)
     t
 end
 
-# ---- compile + integrate ---------------------------------------------------------------------------------
-function compile(t::Tape, order::Integer; mode = 0, kind = 0)
-    GC.@preserve t begin
-        desc = TbOdeDesc(t.dof, t.npar, t.ntmp, length(t.ops), 0, 0, pointer(t.ops), 0, 0, 0, 0, C_NULL)
-        ode = ccall((:tb_ode_create, LIB), Ptr{Cvoid}, (Ref{TbOdeDesc},), desc)
+# ---- compile (cached) --------------------------------------------------------------------------------
+# One kernel per (tape, order, mode, kind, flags); the ode handle is freed as soon as tb_compile has copied it.
+const KIND_PLAIN, KIND_EVENTS = 0, 1
+const CF_FINAL_ONLY = 262144
+const KERNELS = Dict{Tuple{UInt,Int,Int,Int,Int,Int32},Ptr{Cvoid}}()
+function compile(t::Tape, order::Integer; mode = 0, kind = 0, flags = 0, ev_g::Int32 = Int32(0))
+    key = (objectid(t), Int(order), Int(mode), Int(kind), Int(flags), ev_g)
+    haskey(KERNELS, key) && return KERNELS[key]
+    ode = GC.@preserve t begin
+        desc = TbOdeDesc(t.dof, t.npar, t.ntmp, length(t.ops), 0, 0, pointer(t.ops), ev_g, 0, 0, 0, C_NULL)
+        ccall((:tb_ode_create, LIB), Ptr{Cvoid}, (Ref{TbOdeDesc},), desc)
     end
     ode == C_NULL && error("tb_ode_create: " * lasterror())
     co = TbCompileOpts()
     ccall((:tb_compile_opts_default, LIB), Cvoid, (Ref{TbCompileOpts},), co)
-    co.order, co.mode, co.kind = order, mode, kind
+    co.order, co.mode, co.kind, co.flags = order, mode, kind, flags
     k = ccall((:tb_compile, LIB), Ptr{Cvoid}, (Ptr{Cvoid}, Ref{TbCompileOpts}), ode, co)
-    k == C_NULL && error("tb_compile: " * lasterror())
-    k
+    err = k == C_NULL ? lasterror() : ""
+    ccall((:tb_ode_free, LIB), Cvoid, (Ptr{Cvoid},), ode)
+    k == C_NULL && error("tb_compile: " * err)
+    KERNELS[key] = k
+end
+"free every cached kernel (tb_kernel_free)"
+function free_kernels()
+    for k in values(KERNELS); ccall((:tb_kernel_free, LIB), Cvoid, (Ptr{Cvoid},), k); end
+    empty!(KERNELS)
+end
+
+function make_opts(abstol, reltol, minstepsize, maxstepsize, maxsteps, params)
+    o = TbOpts(); ccall((:tb_opts_default, LIB), Cvoid, (Ref{TbOpts},), o)
+    o.abstol, o.reltol, o.minstepsize, o.maxstepsize, o.maxsteps = abstol, reltol, minstepsize, maxstepsize, maxsteps
+    o.params_per_traj = params isa Matrix ? 1 : 0
+    o
+end
+function warn_status(st)  # the reference's warnings: taylorinteg.jl:360-363, 372-377; rootfinding.jl:222-224
+    any(s -> s & ST_MAXSTEPS != 0, st) && @warn "Maximum number of integration steps reached; exiting."
+    any(s -> s & ST_ZERO_STEP != 0, st) && @warn "The step-size is zero; aborting integration."
+    any(s -> s & ST_NR_NOCONV != 0, st) && @warn "Newton-Raphson did not converge for prescribed tolerance and maximum allowed iterations."
 end
 
 """
@@ -133,23 +158,94 @@ major = the ABI's [dof x N] layout). `params` is `npar` (shared) or `N x npar` (
 """
 function taylorinteg(tape::Tape, q0::Matrix{Float64}, t0::Real, tmax::Real, order::Integer, abstol::Real,
                      params::VecOrMat{Float64} = Float64[]; maxsteps::Integer = 500, reltol::Real = 0.0,
-                     minstepsize::Real = 0.0, maxstepsize::Real = Inf, fast::Bool = false)
+                     minstepsize::Real = 0.0, maxstepsize::Real = Inf, fast::Bool = false,
+                     devices = nothing, block::Integer = 4096)
     N, dof = size(q0); dof == tape.dof || throw(ArgumentError("q0 must be N x dof"))
-    k = compile(tape, order; mode = fast ? 1 : 0)
-    o = TbOpts(); ccall((:tb_opts_default, LIB), Cvoid, (Ref{TbOpts},), o)
-    o.abstol, o.reltol, o.minstepsize, o.maxstepsize, o.maxsteps = abstol, reltol, minstepsize, maxstepsize, maxsteps
-    o.params_per_traj = params isa Matrix ? 1 : 0
+    k = compile(tape, order; mode = fast ? 1 : 0, flags = CF_FINAL_ONLY)
+    o = make_opts(abstol, reltol, minstepsize, maxstepsize, maxsteps, params)
     xf = Matrix{Float64}(undef, N, dof); tf = Vector{Float64}(undef, N)
     ns = Vector{Int64}(undef, N); st = Vector{Int32}(undef, N)
     out = TbOut(); out.xfinal, out.tfinal, out.nsteps, out.status = pointer(xf), pointer(tf), pointer(ns), pointer(st)
-    rc = GC.@preserve xf tf ns st ccall((:tb_integrate, LIB), Cint,
-        (Ptr{Cvoid}, Int64, Ptr{Float64}, Ptr{Float64}, Float64, Float64, Ref{TbOpts}, Ref{TbOut}),
-        k, N, q0, params, t0, tmax, o, out)
-    ccall((:tb_kernel_free, LIB), Cvoid, (Ptr{Cvoid},), k)
+    rc = GC.@preserve xf tf ns st q0 params begin
+        if devices === nothing
+            ccall((:tb_integrate, LIB), Cint,
+                  (Ptr{Cvoid}, Int64, Ptr{Float64}, Ptr{Float64}, Float64, Float64, Ref{TbOpts}, Ref{TbOut}),
+                  k, N, q0, params, t0, tmax, o, out)
+        else  # one ensemble over several GPUs of this process (tb_integrate_multi, round-robin blocks)
+            dv = Int32.(devices)
+            ccall((:tb_integrate_multi, LIB), Cint,
+                  (Ptr{Cvoid}, Ptr{Int32}, Int32, Int64, Int64, Ptr{Float64}, Ptr{Float64}, Float64, Float64,
+                   Ptr{Float64}, Int64, Ref{TbOpts}, Ref{TbOut}),
+                  k, dv, length(dv), block, N, q0, params, t0, tmax, C_NULL, 0, o, out)
+        end
+    end
     rc == 0 || error("tb_integrate: " * lasterror())
-    any(s -> s & ST_MAXSTEPS != 0, st) && @warn "Maximum number of integration steps reached; exiting." # taylorinteg.jl:372-377
-    any(s -> s & ST_ZERO_STEP != 0, st) && @warn "The step-size is zero; aborting integration."          # taylorinteg.jl:360-363
+    warn_status(st)
     (xf, tf, ns, st)
 end
+
+"""
+    taylorinteg_trange(tape, q0, trange, order, abstol, params=Float64[]; maxsteps=500, ...)
+
+`taylorinteg(f!, q0, trange, order, abstol, params)` (src/integrator/taylorinteg.jl:558-642) over an ensemble:
+returns `(xv::Array{Float64,3} (N x nt x dof, NaN past the last time reached), xfinal, nsteps, status)`.
+"""
+function taylorinteg_trange(tape::Tape, q0::Matrix{Float64}, trange::AbstractVector{<:Real}, order::Integer,
+                            abstol::Real, params::VecOrMat{Float64} = Float64[]; maxsteps::Integer = 500,
+                            reltol::Real = 0.0, minstepsize::Real = 0.0, maxstepsize::Real = Inf, fast::Bool = false)
+    N, dof = size(q0); dof == tape.dof || throw(ArgumentError("q0 must be N x dof"))
+    tr = collect(Float64, trange); nt = length(tr)
+    @assert nt >= 2 && (issorted(tr) || issorted(tr, rev = true))     # taylorinteg.jl:489,573
+    k = compile(tape, order; mode = fast ? 1 : 0)
+    o = make_opts(abstol, reltol, minstepsize, maxstepsize, maxsteps, params)
+    xv = Array{Float64,3}(undef, N, nt, dof); xf = Matrix{Float64}(undef, N, dof)
+    ns = Vector{Int64}(undef, N); st = Vector{Int32}(undef, N)
+    out = TbOut(); out.xv_trange, out.xfinal, out.nsteps, out.status = pointer(xv), pointer(xf), pointer(ns), pointer(st)
+    rc = GC.@preserve xv xf ns st q0 params tr ccall((:tb_integrate_trange, LIB), Cint,
+        (Ptr{Cvoid}, Int64, Ptr{Float64}, Ptr{Float64}, Ptr{Float64}, Int64, Ref{TbOpts}, Ref{TbOut}),
+        k, N, q0, params, tr, nt, o, out)
+    rc == 0 || error("tb_integrate_trange: " * lasterror())
+    warn_status(st)
+    (xv, xf, ns, st)
+end
+
+"""
+    taylorinteg_events(tape, gcomp, q0, t0, tmax, order, abstol, params=Float64[]; eventorder=0, newtoniter=10,
+                       nrabstol=eps(), event_capacity=maxsteps+1, ...)
+
+`taylorinteg(f!, g, q0, t0, tmax, order, abstol, params)` (src/rootfinding.jl:301-438) for an event function that is a
+state component, `g(dx, x, p, t) = (true, x[gcomp])` (test/rootfinding.jl:26).  Returns
+`(xfinal, tfinal, nsteps, status, tevents (N x cap), xevents (N x cap x dof), gresids (N x cap), nevents)`; only the
+first `nevents[i]` entries of row i are meaningful.
+"""
+function taylorinteg_events(tape::Tape, gcomp::Integer, q0::Matrix{Float64}, t0::Real, tmax::Real, order::Integer,
+                            abstol::Real, params::VecOrMat{Float64} = Float64[]; maxsteps::Integer = 500,
+                            eventorder::Integer = 0, newtoniter::Integer = 10, nrabstol::Real = eps(Float64),
+                            event_capacity::Integer = maxsteps + 1, reltol::Real = 0.0, minstepsize::Real = 0.0,
+                            maxstepsize::Real = Inf, fast::Bool = false)
+    @assert order >= eventorder                                        # rootfinding.jl:321
+    N, dof = size(q0); dof == tape.dof || throw(ArgumentError("q0 must be N x dof"))
+    k = compile(tape, order; mode = fast ? 1 : 0, kind = KIND_EVENTS, ev_g = operand(K_X, gcomp - 1))
+    o = make_opts(abstol, reltol, minstepsize, maxstepsize, maxsteps, params)
+    o.eventorder, o.newtoniter, o.nrabstol, o.event_capacity = eventorder, newtoniter, nrabstol, event_capacity
+    cap = Int(event_capacity)
+    xf = Matrix{Float64}(undef, N, dof); tf = Vector{Float64}(undef, N)
+    ns = Vector{Int64}(undef, N); st = Vector{Int32}(undef, N); ne = Vector{Int32}(undef, N)
+    te = zeros(N, cap); xe = zeros(N, cap, dof); gr = zeros(N, cap)
+    out = TbOut()
+    out.xfinal, out.tfinal, out.nsteps, out.status = pointer(xf), pointer(tf), pointer(ns), pointer(st)
+    out.tevents, out.xevents, out.gresids, out.nevents = pointer(te), pointer(xe), pointer(gr), pointer(ne)
+    rc = GC.@preserve xf tf ns st ne te xe gr q0 params ccall((:tb_integrate, LIB), Cint,
+        (Ptr{Cvoid}, Int64, Ptr{Float64}, Ptr{Float64}, Float64, Float64, Ref{TbOpts}, Ref{TbOut}),
+        k, N, q0, params, t0, tmax, o, out)
+    rc == 0 || error("tb_integrate: " * lasterror())
+    warn_status(st)
+    (xf, tf, ns, st, te, xe, gr, ne)
+end
+
+# lyap_taylorinteg (src/lyapunovspectrum.jl:293-338): the column-parallel kernel (TB_KIND_LYAPCOL) integrates the column
+# system [x; v], v' = J(x) v, which the Python host derives from the tape by first-order forward mode
+# (taylorintegration.jl_b200/tape.py lyap_column_tape).  A Julia caller passes that tape (same TbOp records) to
+# `compile(tape, order; kind = 3)` and calls tb_integrate with `out.lambda`; the tracer above does not build it yet.
 
 end # module
