@@ -259,7 +259,9 @@ class Jet(Workload):
         if which == "5a":
             self.metric, self.default_n, self.nvars, self.dof = "jet_transport_pendulum_n2_d8_trajectory_steps_per_s", 1 << 16, 2, 2
         else:
-            self.metric, self.default_n, self.nvars, self.dof = "jet_transport_kepler_n4_d8_trajectory_steps_per_s", 1 << 16, 4, 4
+            # BASELINE: 2^16 neighbourhoods "sharded across 8 B200" = 8192 per GPU; the default one-GPU line uses 2048
+            # (20 s per pass at ~1.9e4 steps/s) so that W + K passes stay within minutes; --ntraj 8192 is the per-GPU shard
+            self.metric, self.default_n, self.nvars, self.dof = "jet_transport_kepler_n4_d8_trajectory_steps_per_s", 2048, 4, 4
         super().__init__(a)
         from taylorintegration_b200 import problems as P
         import taylorintegration_b200 as tb
@@ -437,7 +439,8 @@ def run_b200(a):
         # fused kernel (CUDA events inside the library, inputs resident at that point), `e2e` the whole call
         d_o = None
         if wide:
-            k = tb.get_wide_kernel(w.tape, w.order, mode)
+            from taylorintegration_b200.api import get_wide_kernel
+            k = get_wide_kernel(w.tape, w.order, mode)
             kname = "tb_wide_kernel"
             info = k.info()
             h_out = out_struct(h_o)

@@ -185,7 +185,7 @@ typedef struct tb_compile_opts {
     int32_t tmem_budget;   /* with TB_CF_TMEM: doubles of jet storage in tensor memory per trajectory (0 = as many as fit) */
 } tb_compile_opts_t;
 #define TB_CF_NO_DISK_CACHE 1 /* do not read/write the on-disk cubin cache    */
-#define TB_CF_KEEP_SOURCE 2   /* (always on) keep generated source for tb_get_source */
+#define TB_CF_TMEM_TAILS 2    /* parity TB_KIND_PLAIN + TB_CF_FINAL_ONLY: state jets that only Horner / the step size read live in tensor memory */
 #define TB_CF_ROLLED 4        /* force kernel variant 1 (rolled loops, all jets in shared memory) */
 /* tuning switches of the unrolled generator (variant 2); all default off */
 #define TB_CF_NO_MEMBAR 8     /* no compiler memory barrier between recurrence groups */

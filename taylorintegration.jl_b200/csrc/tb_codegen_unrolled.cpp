@@ -101,6 +101,7 @@ struct UGen {
     }
     bool derive_x = true;
     bool split = false;   /* registers hold the LOW coefficients of every recurrence-read series (see analyse) */
+    bool tmem_tails = false; /* TB_CF_TMEM_TAILS */
     int top_trim = 0;     /* register series keep coefficients 0..len-1-top_trim in registers, the rest in shared memory */
     bool trim_x = false;  /* parity: do not store x[0], x[1], x[2] of state jets that only Horner / stepsize read */
     int smem_doubles = 0; /* shared-memory doubles per trajectory */
@@ -158,11 +159,15 @@ struct UGen {
                  * (coefficient j only at orders >= j); keeping them in shared memory costs a few loads and hands the
                  * registers to ptxas, whose schedule of the dependent DMUL -> DADD chains is register-starved */
                 si.place = PL_REG; si.id = nreg++; used += si.len; si.kreg = std::max(1, si.len - top_trim);
-            } else if (si.reads > 0 && !state && !no_tmem.count(pr.second) && tused + si.len <= tmem_budget) {
-                si.place = PL_TMEM; si.id = ntm++; si.tbase = tused; tused += si.len;
+            } else if (!tmem_tails && si.reads > 0 && !state && !no_tmem.count(pr.second) && tused + si.len <= tmem_budget) {
+                si.place = PL_TMEM; si.id = ntm++; tused += si.len;
+            } else if (tmem_tails && state && si.reads <= 0 && tused + si.len <= tmem_budget) {
+                /* TB_CF_TMEM_TAILS: the state jets that only Horner and the step size read (written once and read
+                 * once per step) go to tensor memory; shared memory is left to the recurrence-read series and to the
+                 * top coefficients of the register series, which is what lets more than 256 threads share an SM */
+                si.place = PL_TMEM; si.id = ntm++; tused += si.len;
             } else { si.place = PL_SMEM; si.id = nsm++; }
         }
-        tmem_doubles = tused;
         if (split) {
             /* Split placement.  Coefficient j of a series read by recurrences is read P - j times per step, so the
              * top coefficients are cold: the register budget is spread over the LOW coefficients of ALL such series
@@ -187,7 +192,7 @@ struct UGen {
             for (int c = 0; c < d.dof; c++) {
                 int32_t x = TB_OPERAND(TB_K_X, c), dx = TB_OPERAND(TB_K_DX, c);
                 SeriesInfo &si = ser[x];
-                if (si.place != PL_SMEM || si.reads > 0 || !ser.count(dx) || ser[dx].place == PL_NONE || ser[dx].place == PL_DERIVED || ser[dx].place == PL_TMEM) continue;
+                if ((si.place != PL_SMEM && si.place != PL_TMEM) || si.reads > 0 || !ser.count(dx) || ser[dx].place == PL_NONE || ser[dx].place == PL_DERIVED || ser[dx].place == PL_TMEM) continue;
                 if (ser[dx].reads <= 0) continue;
                 si.trim = 3;
                 si.dx = dx;
@@ -208,6 +213,14 @@ struct UGen {
             run += si.len - si.kreg;
         }
         smem_doubles = run;
+        int trun = 0;
+        for (auto &kv : ser) {
+            SeriesInfo &si = kv.second;
+            if (si.place != PL_TMEM) continue;
+            si.tbase = trun - si.trim;
+            trun += si.len - si.trim;
+        }
+        tmem_doubles = trun;
     }
     std::string sref(const SeriesInfo &si, const std::string &k) const { return fmt("SB(%d, %s)", si.base, k.c_str()); }
     std::string sref(const SeriesInfo &si, int k) const { return fmt("SB(%d, %d)", si.base, k); }
@@ -717,7 +730,7 @@ struct UGen {
         if (it == ser.end()) return;
         if (it->second.place == PL_REG && k < it->second.kreg) e.line("  J.r%d[%d] = %s;", it->second.id, k, v.c_str());
         else if (it->second.place == PL_REG) e.line("  %s = %s;", sref(it->second, k).c_str(), v.c_str());
-        else if (it->second.place == PL_TMEM) { e.line("  TB_TM_ST(%d, %s);", 2 * (it->second.tbase + k), v.c_str()); tm_dirty = true; }
+        else if (it->second.place == PL_TMEM) { if (k >= it->second.trim) { e.line("  TB_TM_ST(%d, %s);", 2 * (it->second.tbase + k), v.c_str()); tm_dirty = true; } }
         else if (it->second.place == PL_SMEM && k >= it->second.trim) e.line("  %s = %s;", sref(it->second, k).c_str(), v.c_str());
     }
 
@@ -847,11 +860,13 @@ struct UGen {
             const SeriesInfo &si = ser[TB_OPERAND(TB_K_X, c)];
             if (si.place == PL_REG) e.line("    case %d: return %s;", c, dynref(si, "k").c_str());
             else if (si.place == PL_SMEM && si.trim == 0) e.line("    case %d: return %s;", c, sref(si, "k").c_str());
-            else if (si.place == PL_SMEM) {
+            else if (si.place == PL_TMEM && si.trim == 0) e.line("    case %d: return tb_tm_ld(J.tm + 2 * (%d + k));", c, si.tbase);
+            else if (si.place == PL_SMEM || si.place == PL_TMEM) {
                 const SeriesInfo &di = ser[si.dx];
                 std::string r0 = dynref(di, "0"), r1 = dynref(di, "1");
+                std::string hi = si.place == PL_SMEM ? sref(si, "k") : fmt("tb_tm_ld(J.tm + 2 * (%d + k))", si.tbase);
                 e.line("    case %d: return k == 0 ? x0[%d] : (k == 1 ? M_(%s, 1.0) : (k == 2 ? M_(%s, 0.5) : %s));", c, c, r0.c_str(),
-                       r1.c_str(), sref(si, "k").c_str());
+                       r1.c_str(), hi.c_str());
             } else {
                 const SeriesInfo &di = ser[TB_OPERAND(TB_K_DX, c)];
                 std::string ref = dynref(di, "(k - 1)");
@@ -921,7 +936,8 @@ int generate_unrolled(const Ode &ode, const tb_compile_opts_t &co, Layout &L, st
      * share a lane quadrant split the columns: 256 threads -> 256 columns = 128 doubles per thread.  TB_CF_TMEM
      * turns the tier on (plain kernels; the jet body of the event / team kernels runs in divergent code).        */
     int tmem_budget = 0;
-    if ((co.flags & TB_CF_TMEM) && co.kind == TB_KIND_PLAIN) {
+    g.tmem_tails = (co.flags & TB_CF_TMEM_TAILS) && co.kind == TB_KIND_PLAIN && (co.flags & TB_CF_FINAL_ONLY) && parity;
+    if (((co.flags & TB_CF_TMEM) || g.tmem_tails) && co.kind == TB_KIND_PLAIN) {
         const int btmax = co.block_threads > 0 ? co.block_threads : 256;
         const int share = ((btmax + 31) / 32 + 3) / 4;
         tmem_budget = (512 / share) / 2;
@@ -941,7 +957,7 @@ int generate_unrolled(const Ode &ode, const tb_compile_opts_t &co, Layout &L, st
         bt = (int)(smem_max / per_traj) / 32 * 32;
         if (bt > 256) bt = 256;
     }
-    if (bt < 32 || (bt % 32) || (size_t)bt * per_traj > smem_max) {
+    if (bt < 32 || bt > 512 || (bt % 32) || (size_t)bt * per_traj > smem_max) {
         err = "working set does not fit one warp in shared memory";
         return TB_ERR_UNSUPPORTED;
     }
@@ -988,7 +1004,7 @@ int generate_unrolled(const Ode &ode, const tb_compile_opts_t &co, Layout &L, st
         for (auto &kv : g.ser) if (kv.second.place == PL_REG && kv.second.id == i) kr = kv.second.kreg;
         e.line("  double r%d[%d];", i, kr);
     }
-    if (g.nreg == 0) e.line("  int unused;");
+    e.line("  unsigned tm; /* this warp's tensor-memory window (TB_TMEM kernels) */");
     e.line("};");
     g.emit_jets(e);
     g.emit_accessor(e);

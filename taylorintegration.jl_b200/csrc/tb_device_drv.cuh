@@ -192,11 +192,16 @@ __device__ __forceinline__ double tb_u_stepsize(const TbJets &J, const double *_
         hp.a = 0.0; hp.b = 0.0;
         if (both) hp = tb_stepsize_pair(mk2[0], mk2[1], a.abstol);
 #endif
+        double acs[2][TB_NQ]; /* every coefficient is read before the first data-dependent branch (tensor-memory loads are warp-collective) */
+#pragma unroll
+        for (int j = 0; j < 2; j++)
+#pragma unroll
+            for (int c = 0; c < TB_NQ; c++) acs[j][c] = fabs(TB_X(c, TB_P - 1 + j));
 #pragma unroll
         for (int k = TB_P - 1; k <= TB_P; k++) {
             double m = 0.0, ac[TB_NQ];
 #pragma unroll
-            for (int c = 0; c < TB_NQ; c++) { ac[c] = fabs(TB_X(c, k)); m = fmax(m, ac[c]); anynan = anynan || (ac[c] != ac[c]); }
+            for (int c = 0; c < TB_NQ; c++) { ac[c] = acs[k - (TB_P - 1)][c]; m = fmax(m, ac[c]); anynan = anynan || (ac[c] != ac[c]); }
             if (m != 0.0) {
 #if TB_STEPSIZE_PAIR
                 double hk = both ? (k == TB_P ? hp.b : hp.a) : tb_stepsize_k(m, a.abstol, k);
@@ -214,12 +219,15 @@ __device__ __forceinline__ double tb_u_stepsize(const TbJets &J, const double *_
     } else
 #endif
     {
+        double xa[3][TB_NQ];
+#pragma unroll
+        for (int c = 0; c < TB_NQ; c++) { xa[0][c] = fabs(TB_X(c, 0)); xa[1][c] = fabs(TB_X(c, TB_P - 1)); xa[2][c] = fabs(TB_X(c, TB_P)); }
 #pragma unroll
         for (int c = 0; c < TB_NQ; c++) {
-            const double x0norm = fabs(TB_X(c, 0));
+            const double x0norm = xa[0][c];
 #pragma unroll
             for (int k = TB_P - 1; k <= TB_P; k++) {
-                const double aux = fabs(TB_X(c, k));
+                const double aux = xa[1 + k - (TB_P - 1)][c];
                 if (aux == 0.0) continue;
                 const double rel = M_(a.reltol, x0norm);
                 const double eps = (a.abstol >= rel) ? a.abstol : rel;
@@ -227,15 +235,24 @@ __device__ __forceinline__ double tb_u_stepsize(const TbJets &J, const double *_
             }
         }
     }
-    if (h == TB_INF) { /* all last coefficients vanish: second step-size control */
-        h = 0.0;
+    const bool need2 = h == TB_INF; /* all last coefficients vanish: second step-size control */
+#if TB_TMEM
+    if (__any_sync(0xffffffffu, need2)) { /* the coefficient reads below may be warp-collective: the whole warp takes the branch */
+#else
+    if (need2) {
+#endif
+        double h2 = 0.0;
         double buf[TB_P + 1];
 #pragma unroll
         for (int c = 0; c < TB_NQ; c++) {
 #pragma unroll
             for (int k = 0; k <= TB_P; k++) buf[k] = TB_X(c, k);
-            h = tb_jmax(h, tb_second_stepsize_arr(buf));
+            if (need2) h2 = tb_jmax(h2, tb_second_stepsize_arr(buf));
         }
+        if (need2) h = h2;
+#if TB_TMEM
+        __syncwarp();
+#endif
     }
     h = (h < a.minstep) ? a.minstep : ((h > a.maxstep) ? a.maxstep : h);
     return h;
@@ -422,6 +439,7 @@ __device__ __forceinline__ bool tb_traj_init(TbTraj &T, double *__restrict__ smt
         T.g_old = TB_EV_G0(T.x0);
     } else { /* variant 2: g is a state component (generated accessors), jets in registers / shared memory */
         TbJets J;
+        J.tm = 0u;
         const double *x0 = T.x0;
         tb_u_jets(J, smt, 0u, T.par, T.t0, x0);
         T.f_old = TB_EV_GATE_EXPR;
@@ -448,7 +466,7 @@ __device__ __forceinline__ bool tb_traj_init(TbTraj &T, double *__restrict__ smt
 #define TB_XCOEF(c, k) S((c), (k))
 #define TB_UNROLL_V2
 #else
-#define TB_JETS_DECL TbJets J; const double *x0 = T.x0;
+#define TB_JETS_DECL TbJets J; J.tm = tb_tm; const double *x0 = T.x0;
 #define TB_JETS_ARGS J, smt, x0
 #define TB_JETS_PARAMS const TbJets &J, const double *__restrict__ smt, const double *__restrict__ x0
 #define TB_COMPUTE_JETS(T) tb_u_jets(J, smt, tb_tm, (T).par, (T).t0, x0)
@@ -488,6 +506,20 @@ __device__ __forceinline__ bool tb_traj_step(TbTraj &T, double *__restrict__ smt
     /* taylorinteg!: src/integrator/taylorinteg.jl:356-378 (t0,tmax) and 607-639 (trange) */
     TB_JETS_DECL
     TB_COMPUTE_JETS(T); /* block-lockstep build (TB_BAR): idle lanes run the jets too, for the barriers inside */
+#if TB_TMEM && TB_FINAL_ONLY
+    /* tensor-memory kernels: state jets may live in TMEM, whose loads are warp-collective, so the step size and Horner
+     * run on every lane of the (converged) warp; idle lanes and zero steps are sorted out afterwards                 */
+    double dt = TB_STEPSIZE(a);
+    const bool zero_step = dt == 0.0;
+    const double rem = B_(T.tmax, T.t0);
+    dt = M_(T.sign, TB_DTMIN(dt, M_(T.sign, rem)));
+    __syncwarp();
+    double xn[TB_DOF];
+#pragma unroll
+    for (int c = 0; c < TB_DOF; c++) xn[c] = TB_HORNER(c, dt);
+    if (!live) return false;
+    if (zero_step) { T.st |= TB_ST_ZERO_STEP; return true; }
+#else
     if (!live) return false;
     double dt = TB_STEPSIZE(a);
     if (dt == 0.0) { T.st |= TB_ST_ZERO_STEP; return true; }
@@ -496,6 +528,7 @@ __device__ __forceinline__ bool tb_traj_step(TbTraj &T, double *__restrict__ smt
     double xn[TB_DOF];
 #pragma unroll
     for (int c = 0; c < TB_DOF; c++) xn[c] = TB_HORNER(c, dt);
+#endif
 #if TB_FINAL_ONLY
     /* final-state build (TB_CF_FINAL_ONLY): no output grid, no per-step or dense output in the step body; the host
      * refuses such requests for this kernel.  Code that is only disabled at run time still costs the jets' scheduler
@@ -999,11 +1032,14 @@ extern "C" __global__ void __launch_bounds__(TB_BT, TB_MINB) tb_jet_kernel(const
         TB_COMPUTE_JETS(T);
         double dt = TB_STEPSIZE(a);
         if (a.dtout && live) a.dtout[i] = dt;
-        if (a.xjet && live) {
+        if (a.xjet) {
             TB_UNROLL_V2
             for (int c = 0; c < TB_DOF; c++) {
                 TB_UNROLL_V2
-                for (int k = 0; k <= TB_P; k++) a.xjet[((long long)c * TB_NP1 + k) * a.N + i] = TB_XCOEF(c, k);
+                for (int k = 0; k <= TB_P; k++) {
+                    const double v = TB_XCOEF(c, k); /* read by every lane (may be a warp-collective load) */
+                    if (live) a.xjet[((long long)c * TB_NP1 + k) * a.N + i] = v;
+                }
             }
         }
     }

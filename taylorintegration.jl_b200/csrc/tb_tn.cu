@@ -50,6 +50,8 @@ struct TnArgs {
     const int *pair_off;          /* [nc+1] */
     const unsigned short *pair_a; /* pairs of slot m, ascending ia */
     const unsigned short *pair_b;
+    const unsigned int *pair_ab; /* ia | ib << 16: one load per pair */
+    int npairs, pairs_in_smem;
     const double *q0;     /* [dof x nc x N] */
     const double *params; /* [npar x N] or [npar] */
     const double *trange;
@@ -85,28 +87,70 @@ struct Jets {
     __device__ __forceinline__ double *co(int o, int k) const { return ser(o) + (size_t)k * nc; }
 };
 
-/* acc += sum over the pairs [p0, p1) of slot m of (f*U[ia]) * V[ib] */
+/* acc += sum over the pairs [p0, p1) of slot m of (f*U[ia]) * V[ib]; U and V are polynomials STAGED IN SHARED MEMORY
+ * (random 8-byte gathers from the L2-resident workspace cost a 32-byte sector each and made the n = 4 kernel L2-bound) */
 template <bool FAST>
 __device__ __forceinline__ double gather(double acc, const TnArgs &a, int p0, int p1, const double *__restrict__ U,
                                          const double *__restrict__ V, bool hasf, double f) {
-    for (int p = p0; p < p1; p++) {
-        const int ia = __ldg(a.pair_a + p), ib = __ldg(a.pair_b + p);
-        double u = U[ia];
-        if (hasf) u = __dmul_rn(f, u);
-        acc = mad<FAST>(u, V[ib], acc);
+    const unsigned int *__restrict__ pab = a.pair_ab;
+    if (hasf) {
+        for (int p = p0; p < p1; p++) {
+            const unsigned int ab = pab[p];
+            acc = mad<FAST>(__dmul_rn(f, U[ab & 0xffffu]), V[ab >> 16], acc);
+        }
+    } else {
+#pragma unroll 4
+        for (int p = p0; p < p1; p++) {
+            const unsigned int ab = pab[p];
+            acc = mad<FAST>(U[ab & 0xffffu], V[ab >> 16], acc);
+        }
+    }
+    return acc;
+}
+
+/* Time-index sum of polynomial products, sum_{i = ilo..ihi} (f_i U_i) * V_i, operands staged through shared memory:
+ * while the CTA gathers from one pair of buffers every thread copies ITS coefficient of the next operands into the
+ * other pair (coalesced reads of the workspace), one barrier per i.  term(i, U, V, hasf, f) names the operands.    */
+template <bool FAST, class F>
+__device__ __forceinline__ double staged_sum(double acc, const TnArgs &a, double *__restrict__ stg, int m, bool act, int p0, int p1,
+                                             int ilo, int ihi, F term) {
+    const int nc = a.nc;
+    const double *U, *V;
+    bool hasf; double f;
+    int buf = 0;
+    if (ilo <= ihi) {
+        term(ilo, U, V, hasf, f);
+        if (act) { stg[m] = U[m]; stg[nc + m] = V[m]; }
+    }
+    __syncthreads();
+    for (int i = ilo; i <= ihi; i++) {
+        term(i, U, V, hasf, f);
+        const bool hf = hasf; const double ff = f;
+        if (i < ihi) {
+            term(i + 1, U, V, hasf, f);
+            if (act) { stg[(2 * (buf ^ 1)) * nc + m] = U[m]; stg[(2 * (buf ^ 1) + 1) * nc + m] = V[m]; }
+        }
+        if (act) acc = gather<FAST>(acc, a, p0, p1, stg + (2 * buf) * nc, stg + (2 * buf + 1) * nc, hf, ff);
+        __syncthreads();
+        buf ^= 1;
     }
     return acc;
 }
 
 /* Q = Nn / B over homogeneous degree; nn = Nn[m] in a register.  Q_g = (Nn_g - sum_{j<g} Q_j B_{g-j}) / B_0 */
 template <bool FAST>
-__device__ void tn_div(const TnArgs &a, int m, int degm, double *Q, double nn, const double *B) {
+__device__ void tn_div(const TnArgs &a, int m, int degm, double *Q, double nn, const double *B, double *__restrict__ stg) {
     const bool act = m < a.nc;
+    double *sQ = stg, *sB = stg + a.nc;
+    if (act) sB[m] = B[m];
+    __syncthreads();
     const int p0 = act ? a.pair_off[m] : 0, p1 = act ? a.pair_off[m + 1] - 1 : 0; /* last pair is (m, 0) */
     for (int g = 0; g <= a.d; g++) {
         if (act && degm == g) {
-            const double t = gather<FAST>(0.0, a, p0, p1, Q, B, false, 0.0);
-            Q[m] = __ddiv_rn(__dsub_rn(nn, t), B[0]);
+            const double t = gather<FAST>(0.0, a, p0, p1, sQ, sB, false, 0.0);
+            const double q = __ddiv_rn(__dsub_rn(nn, t), sB[0]);
+            sQ[m] = q;
+            Q[m] = q;
         }
         __syncthreads();
     }
@@ -114,21 +158,27 @@ __device__ void tn_div(const TnArgs &a, int m, int degm, double *Q, double nn, c
 
 /* C = A^r: C_0 = A_0^r; C_g = sum_{j<g} ((r(g-j) - j) C_j) A_{g-j} / (g A_0) */
 template <bool FAST>
-__device__ void tn_pow(const TnArgs &a, int m, int degm, double *C, const double *A, double r) {
+__device__ void tn_pow(const TnArgs &a, int m, int degm, double *C, const double *A, double r, double *__restrict__ stg) {
     const bool act = m < a.nc;
-    if (m == 0) C[0] = tb_pow(A[0], r);
+    double *sC = stg, *sA = stg + a.nc;
+    if (act) sA[m] = A[m];
+    __syncthreads();
+    if (m == 0) { const double c0 = tb_pow(sA[0], r); sC[0] = c0; C[0] = c0; }
     __syncthreads();
     const int p0 = act ? a.pair_off[m] : 0, p1 = act ? a.pair_off[m + 1] - 1 : 0;
     for (int g = 1; g <= a.d; g++) {
         if (act && degm == g) {
             double t = 0.0;
             for (int p = p0; p < p1; p++) {
-                const int ia = __ldg(a.pair_a + p), ib = __ldg(a.pair_b + p);
+                const unsigned int ab = a.pair_ab[p];
+                const int ia = ab & 0xffffu, ib = ab >> 16;
                 const int j = a.deg[ia];
                 const double f = __dsub_rn(__dmul_rn(r, (double)(g - j)), (double)j);
-                t = mad<FAST>(__dmul_rn(f, C[ia]), A[ib], t);
+                t = mad<FAST>(__dmul_rn(f, sC[ia]), sA[ib], t);
             }
-            C[m] = __ddiv_rn(t, __dmul_rn((double)g, A[0]));
+            const double c = __ddiv_rn(t, __dmul_rn((double)g, sA[0]));
+            sC[m] = c;
+            C[m] = c;
         }
         __syncthreads();
     }
@@ -136,24 +186,29 @@ __device__ void tn_pow(const TnArgs &a, int m, int degm, double *C, const double
 
 /* S = sin A, Cc = cos A: S_g = sum_{j>=1} (j A_j) Cc_{g-j} / g, Cc_g = -sum_{j>=1} (j A_j) S_{g-j} / g */
 template <bool FAST>
-__device__ void tn_sincos(const TnArgs &a, int m, int degm, double *S, double *Cc, const double *A) {
+__device__ void tn_sincos(const TnArgs &a, int m, int degm, double *S, double *Cc, const double *A, double *__restrict__ stg) {
     const bool act = m < a.nc;
-    if (m == 0) { double s, c; tb_sincos(A[0], &s, &c); S[0] = s; Cc[0] = c; }
+    double *sS = stg, *sC = stg + a.nc, *sA = stg + 2 * a.nc;
+    if (act) sA[m] = A[m];
+    __syncthreads();
+    if (m == 0) { double s, c; tb_sincos(sA[0], &s, &c); sS[0] = s; sC[0] = c; S[0] = s; Cc[0] = c; }
     __syncthreads();
     const int p0 = act ? a.pair_off[m] + 1 : 0, p1 = act ? a.pair_off[m + 1] : 0; /* first pair is (0, m) */
     for (int g = 1; g <= a.d; g++) {
         if (act && degm == g) {
             double ts = 0.0, tc = 0.0;
             for (int p = p0; p < p1; p++) {
-                const int ia = __ldg(a.pair_a + p), ib = __ldg(a.pair_b + p);
+                const unsigned int ab = a.pair_ab[p];
+                const int ia = ab & 0xffffu, ib = ab >> 16;
                 const int j = a.deg[ia];
-                double u = A[ia];
+                double u = sA[ia];
                 if (j >= 2) u = __dmul_rn((double)j, u);
-                ts = mad<FAST>(u, Cc[ib], ts);
-                tc = mad<FAST>(u, S[ib], tc);
+                ts = mad<FAST>(u, sC[ib], ts);
+                tc = mad<FAST>(u, sS[ib], tc);
             }
-            S[m] = __ddiv_rn(ts, (double)g);
-            Cc[m] = __ddiv_rn(-tc, (double)g);
+            const double sv = __ddiv_rn(ts, (double)g), cv = __ddiv_rn(-tc, (double)g);
+            sS[m] = sv; sC[m] = cv;
+            S[m] = sv; Cc[m] = cv;
         }
         __syncthreads();
     }
@@ -161,7 +216,7 @@ __device__ void tn_sincos(const TnArgs &a, int m, int degm, double *S, double *C
 
 /* one tape entry at time order k; every thread of the CTA calls it; ends with a barrier */
 template <bool FAST>
-__device__ void run_op(const TnArgs &a, const Jets &J, const double *par, double *scratch, const tb_op_t &op, int k,
+__device__ void run_op(const TnArgs &a, const Jets &J, const double *par, double *scratch, double *stg, const tb_op_t &op, int k,
                        int m, int degm) {
     const int ka = TB_OPERAND_KIND(op.a), kb = TB_OPERAND_KIND(op.b);
     const bool sa = ka == TB_K_PAR || ka == TB_K_IMM, sb = kb == TB_K_PAR || kb == TB_K_IMM;
@@ -195,69 +250,63 @@ __device__ void run_op(const TnArgs &a, const Jets &J, const double *par, double
             }
             break;
         case TB_OP_MUL:
-            if (act) {
-                if (sa && sb) R[m] = (k == 0 && m == 0) ? __dmul_rn(na, nb) : 0.0;
-                else if (sa || sb) R[m] = __dmul_rn(sa ? na : nb, J.co(sa ? op.b : op.a, k)[m]);
-                else {
-                    double acc = 0.0;
-                    for (int i = 0; i <= k; i++) acc = gather<FAST>(acc, a, p0, p1, J.co(op.a, i), J.co(op.b, k - i), false, 0.0);
-                    R[m] = acc;
-                }
+            if (sa && sb) { if (act) R[m] = (k == 0 && m == 0) ? __dmul_rn(na, nb) : 0.0; }
+            else if (sa || sb) { if (act) R[m] = __dmul_rn(sa ? na : nb, J.co(sa ? op.b : op.a, k)[m]); }
+            else {
+                const double acc = staged_sum<FAST>(0.0, a, stg, m, act, p0, p1, 0, k,
+                    [&](int i, const double *&U, const double *&V, bool &hf, double &f) { U = J.co(op.a, i); V = J.co(op.b, k - i); hf = false; f = 0.0; });
+                if (act) R[m] = acc;
             }
             break;
-        case TB_OP_SQR:
-            if (act) {
-                double acc = 0.0;
-                if (k == 0) acc = gather<FAST>(acc, a, p0, p1, J.co(op.a, 0), J.co(op.a, 0), false, 0.0);
-                else {
-                    const int kodd = k & 1, kend = (k - 2 + kodd) / 2;
-                    for (int i = 0; i <= kend; i++) acc = gather<FAST>(acc, a, p0, p1, J.co(op.a, i), J.co(op.a, k - i), false, 0.0);
-                    acc = __dmul_rn(2.0, acc);
-                    if (!kodd) acc = gather<FAST>(acc, a, p0, p1, J.co(op.a, k / 2), J.co(op.a, k / 2), false, 0.0);
-                }
-                R[m] = acc;
+        case TB_OP_SQR: {
+            const int kodd = k & 1, kend = k == 0 ? 0 : (k - 2 + kodd) / 2;
+            double acc = staged_sum<FAST>(0.0, a, stg, m, act, p0, p1, 0, kend,
+                [&](int i, const double *&U, const double *&V, bool &hf, double &f) { U = J.co(op.a, i); V = J.co(op.a, k - i); hf = false; f = 0.0; });
+            if (k > 0) {
+                acc = __dmul_rn(2.0, acc);
+                if (!kodd) acc = staged_sum<FAST>(acc, a, stg, m, act, p0, p1, k / 2, k / 2,
+                    [&](int i, const double *&U, const double *&V, bool &hf, double &f) { U = J.co(op.a, i); V = J.co(op.a, i); hf = false; f = 0.0; });
             }
+            if (act) R[m] = acc;
             break;
+        }
         case TB_OP_DIV:
             if (sb) {
                 if (act) R[m] = sa ? ((k == 0 && m == 0) ? __ddiv_rn(na, nb) : 0.0) : __ddiv_rn(J.co(op.a, k)[m], nb);
             } else {
+                const double t = staged_sum<FAST>(0.0, a, stg, m, act, p0, p1, 0, k - 1,
+                    [&](int i, const double *&U, const double *&V, bool &hf, double &f) { U = J.co(op.res, i); V = J.co(op.b, k - i); hf = false; f = 0.0; });
                 double nn = 0.0;
                 if (act) {
-                    double t = 0.0;
-                    for (int i = 0; i < k; i++) t = gather<FAST>(t, a, p0, p1, J.co(op.res, i), J.co(op.b, k - i), false, 0.0);
                     const double num = sa ? ((k == 0 && m == 0) ? na : 0.0) : J.co(op.a, k)[m];
                     nn = __dsub_rn(num, t);
                 }
-                tn_div<FAST>(a, m, degm, R, nn, J.co(op.b, 0));
+                tn_div<FAST>(a, m, degm, R, nn, J.co(op.b, 0), stg);
             }
             break;
         case TB_OP_POW:
-            if (k == 0) tn_pow<FAST>(a, m, degm, R, J.co(op.a, 0), op.imm);
+            if (k == 0) tn_pow<FAST>(a, m, degm, R, J.co(op.a, 0), op.imm, stg);
             else {
-                double t = 0.0;
-                if (act) {
-                    for (int i = 0; i < k; i++) {
-                        const double f = __dsub_rn(__dmul_rn(op.imm, (double)(k - i)), (double)i);
-                        t = gather<FAST>(t, a, p0, p1, J.co(op.res, i), J.co(op.a, k - i), true, f);
-                    }
-                    scratch[m] = __dmul_rn((double)k, J.co(op.a, 0)[m]);
-                }
+                const double t = staged_sum<FAST>(0.0, a, stg, m, act, p0, p1, 0, k - 1,
+                    [&](int i, const double *&U, const double *&V, bool &hf, double &f) {
+                        U = J.co(op.res, i); V = J.co(op.a, k - i); hf = true;
+                        f = __dsub_rn(__dmul_rn(op.imm, (double)(k - i)), (double)i);
+                    });
+                if (act) scratch[m] = __dmul_rn((double)k, J.co(op.a, 0)[m]);
                 __syncthreads();
-                tn_div<FAST>(a, m, degm, R, t, scratch);
+                tn_div<FAST>(a, m, degm, R, t, scratch, stg);
             }
             break;
         case TB_OP_SINCOS: {
             double *Cc = J.co(op.aux, k);
-            if (k == 0) tn_sincos<FAST>(a, m, degm, R, Cc, J.co(op.a, 0));
-            else if (act) {
-                double ts = 0.0, tc = 0.0;
-                for (int i = 1; i <= k; i++) {
-                    ts = gather<FAST>(ts, a, p0, p1, J.co(op.a, i), J.co(op.aux, k - i), i >= 2, (double)i);
-                    tc = gather<FAST>(tc, a, p0, p1, J.co(op.a, i), J.co(op.res, k - i), i >= 2, (double)i);
-                }
-                R[m] = __ddiv_rn(ts, (double)k);
-                Cc[m] = __ddiv_rn(-tc, (double)k);
+            if (k == 0) tn_sincos<FAST>(a, m, degm, R, Cc, J.co(op.a, 0), stg);
+            else {
+                /* two sums over the same scaled operand (i a_i): staged once per sum (same bits, order unchanged) */
+                const double ts = staged_sum<FAST>(0.0, a, stg, m, act, p0, p1, 1, k,
+                    [&](int i, const double *&U, const double *&V, bool &hf, double &f) { U = J.co(op.a, i); V = J.co(op.aux, k - i); hf = i >= 2; f = (double)i; });
+                const double tc = staged_sum<FAST>(0.0, a, stg, m, act, p0, p1, 1, k,
+                    [&](int i, const double *&U, const double *&V, bool &hf, double &f) { U = J.co(op.a, i); V = J.co(op.res, k - i); hf = i >= 2; f = (double)i; });
+                if (act) { R[m] = __ddiv_rn(ts, (double)k); Cc[m] = __ddiv_rn(-tc, (double)k); }
             }
             break;
         }
@@ -278,10 +327,18 @@ __device__ double block_max(double v, double *red) {
     return r;
 }
 
-template <bool FAST> __global__ void __launch_bounds__(1024) tn_kernel(const TnArgs a) {
+template <bool FAST> __global__ void __launch_bounds__(1024) tn_kernel(const TnArgs a_in) {
     __shared__ double red[32];
     __shared__ unsigned long long s_idx;
-    extern __shared__ double scratch[]; /* [nc] */
+    extern __shared__ double scratch[]; /* [nc] + staging buffers [6][nc] (+ the pair table) */
+    TnArgs a = a_in;
+    double *stg = scratch + a.nc;
+    if (a.pairs_in_smem) { /* the index pairs are read once per product term: keep them next to the operands */
+        unsigned int *sp = (unsigned int *)(scratch + 7 * a.nc);
+        for (int q = threadIdx.x; q < a.npairs; q += blockDim.x) sp[q] = a_in.pair_ab[q];
+        a.pair_ab = sp;
+        __syncthreads();
+    }
     const int m = threadIdx.x, nc = a.nc, P = a.P;
     const bool act = m < nc;
     const int degm = act ? a.deg[m] : -1;
@@ -318,7 +375,7 @@ template <bool FAST> __global__ void __launch_bounds__(1024) tn_kernel(const TnA
             if (m == 0) J.co(TIME, 0)[0] = t0;
             __syncthreads();
             for (int k = 0; k < P; k++) {
-                for (int j = 0; j < a.nops; j++) run_op<FAST>(a, J, par, scratch, a.ops[j], k, m, degm);
+                for (int j = 0; j < a.nops; j++) run_op<FAST>(a, J, par, scratch, stg, a.ops[j], k, m, degm);
                 if (act)
                     for (int c = 0; c < a.dof; c++)
                         J.co(TB_OPERAND(TB_K_X, c), k + 1)[m] = __ddiv_rn(J.co(TB_OPERAND(TB_K_DX, c), k)[m], (double)(k + 1));
@@ -424,6 +481,7 @@ struct tb_tn {
     unsigned char *d_deg = nullptr;
     int *d_off = nullptr;
     unsigned short *d_pa = nullptr, *d_pb = nullptr;
+    unsigned int *d_pab = nullptr;
 };
 
 extern "C" {
@@ -458,7 +516,7 @@ tb_tn_t *tb_tn_create(const tb_ode_t *ode, int order, int nvars, int varorder, i
 
 void tb_tn_free(tb_tn_t *t) {
     if (!t) return;
-    if (t->d_ops) { cudaFree(t->d_ops); cudaFree(t->d_deg); cudaFree(t->d_off); cudaFree(t->d_pa); cudaFree(t->d_pb); }
+    if (t->d_ops) { cudaFree(t->d_ops); cudaFree(t->d_deg); cudaFree(t->d_off); cudaFree(t->d_pa); cudaFree(t->d_pb); cudaFree(t->d_pab); }
     delete t;
 }
 
@@ -491,10 +549,19 @@ int tb_tn_integrate(tb_tn_t *t, int64_t N, const double *q0, const double *param
         TB_CUDA(cudaMalloc(&t->d_pb, 2 * np));
         TB_CUDA(cudaMemcpy(t->d_pa, t->T.pair_a.data(), 2 * np, cudaMemcpyHostToDevice));
         TB_CUDA(cudaMemcpy(t->d_pb, t->T.pair_b.data(), 2 * np, cudaMemcpyHostToDevice));
+        std::vector<unsigned int> pab(np);
+        for (size_t q = 0; q < np; q++) pab[q] = (unsigned int)t->T.pair_a[q] | ((unsigned int)t->T.pair_b[q] << 16);
+        TB_CUDA(cudaMalloc(&t->d_pab, 4 * (np ? np : 1)));
+        TB_CUDA(cudaMemcpy(t->d_pab, pab.data(), 4 * np, cudaMemcpyHostToDevice));
     }
     const int threads = ((nc + 31) / 32) * 32;
-    const size_t smem = sizeof(double) * nc;
+    size_t smem = sizeof(double) * nc * 7; /* scratch + 6 staging buffers */
+    const size_t npairs = t->T.pair_a.size();
+    const bool pairs_in_smem = smem + 4 * npairs <= 100 * 1024;
+    if (pairs_in_smem) smem += 4 * npairs;
     const bool fast = t->mode == TB_MODE_FAST;
+    if (fast) TB_CUDA(cudaFuncSetAttribute(tn_kernel<true>, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)smem));
+    else TB_CUDA(cudaFuncSetAttribute(tn_kernel<false>, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)smem));
     int bps = 1, nsm = 148;
     if (fast) TB_CUDA(cudaOccupancyMaxActiveBlocksPerMultiprocessor(&bps, tn_kernel<true>, threads, smem));
     else TB_CUDA(cudaOccupancyMaxActiveBlocksPerMultiprocessor(&bps, tn_kernel<false>, threads, smem));
@@ -506,7 +573,7 @@ int tb_tn_integrate(tb_tn_t *t, int64_t N, const double *q0, const double *param
     TnArgs a{};
     a.N = N; a.dof = d.dof; a.npar = d.npar; a.ntmp = d.ntmp; a.nops = d.nops; a.P = P; a.nc = nc; a.d = t->varorder;
     a.nser = 2 * d.dof + d.ntmp + 1;
-    a.ops = t->d_ops; a.deg = t->d_deg; a.pair_off = t->d_off; a.pair_a = t->d_pa; a.pair_b = t->d_pb;
+    a.ops = t->d_ops; a.deg = t->d_deg; a.pair_off = t->d_off; a.pair_a = t->d_pa; a.pair_b = t->d_pb; a.pair_ab = t->d_pab; a.npairs = (int)npairs; a.pairs_in_smem = pairs_in_smem ? 1 : 0;
     a.nt = trange ? nt : 0; a.t0 = t0; a.tmax = tmax; a.abstol = o->abstol; a.reltol = o->reltol;
     a.minstep = o->minstepsize; a.maxstep = o->maxstepsize; a.maxsteps = o->maxsteps; a.params_per_traj = o->params_per_traj;
     const size_t nq = (size_t)d.dof * nc * N, npar = (size_t)(d.npar > 0 ? d.npar : 1) * (o->params_per_traj ? N : 1);
