@@ -180,12 +180,13 @@ def get_kernel(tape: Tape, order: int, kind: int, mode: int, **kw) -> Kernel:
 
 
 def make_opts(abstol=1e-20, reltol=0.0, minstepsize=0.0, maxstepsize=np.inf, maxsteps=500, eventorder=0,
-              newtoniter=10, nrabstol=_EPS, event_capacity=0, params_per_traj=0, steps_stride=0) -> L.TbOpts:
+              newtoniter=10, nrabstol=_EPS, event_capacity=0, params_per_traj=0, steps_stride=0, sort_by_cost=0) -> L.TbOpts:
     o = L.TbOpts()
     L.lib().tb_opts_default(C.byref(o))
     o.abstol, o.reltol, o.minstepsize, o.maxstepsize = float(abstol), float(reltol), float(minstepsize), float(maxstepsize)
     o.maxsteps, o.eventorder, o.newtoniter, o.nrabstol = int(maxsteps), int(eventorder), int(newtoniter), float(nrabstol)
     o.event_capacity, o.params_per_traj, o.steps_stride = int(event_capacity), int(params_per_traj), int(steps_stride)
+    o.sort_by_cost = int(sort_by_cost)
     return o
 
 

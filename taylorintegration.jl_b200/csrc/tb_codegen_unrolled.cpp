@@ -593,6 +593,8 @@ struct UGen {
             }
             case TB_OP_POW:
                 if (fast) e.line("  const double %s = %s * (inv%d * %s);", r, s.c_str(), opi, dlit(1.0 / k).c_str());
+                else if (pow_recip) /* s / (k a[0]) from the reciprocal prepared at the start of the group (emit_group): 3 dependent operations */
+                    e.line("  const double %s = DIVY_(%s, denP%d_%d, invP%d_%d, okP%d_%d);", r, s.c_str(), opi, k, opi, k, opi, k);
                 else { std::string a0 = A(0); e.line("  const double %s = DIVQ_(%s, M_(%s, %s));", r, s.c_str(), dlit((double)k).c_str(), a0.c_str()); }
                 break;
             case TB_OP_EXP:
@@ -629,6 +631,7 @@ struct UGen {
      * term with two warps per scheduler; ncu: the DMUL after each LDS holds 2/3 of the samples of such a chain).
      * Every load of a group reads a coefficient stored by an EARLIER group (val() loads only indices below `cur`), so
      * it may move up to the start of the group: each load line moves `prefetch` lines up, order among loads kept.  */
+    bool pow_recip = false; /* parity: pow! quotients from a reciprocal prepared ahead of the sum (TB_CF_POW_RECIP, opt-in: measured slower) */
     int prefetch = 0;  /* lines a storage load moves up (TB_CF_PREFETCH) */
     int mulahead = 0;  /* lines a product moves up (TB_CF_MULAHEAD) */
     static bool ident_char(char ch) { return (ch >= 'a' && ch <= 'z') || (ch >= 'A' && ch <= 'Z') || (ch >= '0' && ch <= '9') || ch == '_'; }
@@ -697,6 +700,18 @@ struct UGen {
         scaled.clear();
         size_t nchains = 0;
         for (SNode &n : g) { build_chains(n); nchains += n.ch.size(); }
+        if (!fast && pow_recip)
+            for (SNode &n : g) {
+                /* pow!: c[k] = s / (k a[0]).  The divisor is known before the sum starts, so its correctly rounded
+                 * reciprocal is computed here, off the critical path (it overlaps the add chain), and the quotient
+                 * is finished with the Markstein correction: the full division (10 dependent operations between the
+                 * end of this sum and the start of the division sums that wait for r[k]) leaves the chain.       */
+                const tb_op_t &op = ode.ops[n.j];
+                if (eff_op(op) != TB_OP_POW) continue;
+                std::string a0 = val(e, {op.a, 0});
+                e.line("  const double denP%d_%d = M_(%s, %s), invP%d_%d = D_(1.0, denP%d_%d); const bool okP%d_%d = tb_midrange(denP%d_%d); DENCHK_(denP%d_%d);",
+                       n.j, n.k, dlit((double)n.k).c_str(), a0.c_str(), n.j, n.k, n.j, n.k, n.j, n.k, n.j, n.k, n.j, n.k);
+            }
         for (SNode &n : g)
             for (Chain &c : n.ch) c.nacc = fast ? (nchains >= 4 ? 2 : 4) : 1;
         bool progress = true;
@@ -808,7 +823,7 @@ struct UGen {
                 if ((co.flags & 128) && kmin != last_sync_k && (!(co.flags & 2048) || kmin % 4 == 1)) { e.line("  TB_ORDER_SYNC();"); last_sync_k = kmin; }
                 e.line("  /* ---- order %d: %d recurrence chain group ---- */", kmin, (int)g.size());
                 emit_group(e, g);
-                if (!(co.flags & 8)) e.line("  asm volatile(\"\" ::: \"memory\");");
+                e.line("  asm volatile(\"\" ::: \"memory\");");
                 any = true;
             }
             if (!any) { err = "tape has a dependency cycle or an undefined operand (dx not defined?)"; break; }
@@ -926,6 +941,7 @@ int generate_unrolled(const Ode &ode, const tb_compile_opts_t &co, Layout &L, st
     g.trim_x = parity && co.kind == TB_KIND_PLAIN && !(co.flags & 4096);
     g.split = (co.flags & 8192) != 0;
     g.top_trim = (co.flags >> 20) & 15; /* TB_CF_TOPTRIM(t) */
+    g.pow_recip = (co.flags & TB_CF_POW_RECIP) != 0;
     g.prefetch = (co.flags >> 24) & 15; /* TB_CF_PREFETCH(d) */
     g.mulahead = parity ? (co.flags >> 28) & 7 : 0; /* TB_CF_MULAHEAD(d), lines = 2*d */
     /* default of the parity plain / team kernels (B200 sweep, round 2: Kepler-28 +5 %, Lorenz column kernel +1.6 %,

@@ -197,12 +197,44 @@ __device__ __forceinline__ double tb_u_stepsize(const TbJets &J, const double *_
         for (int j = 0; j < 2; j++)
 #pragma unroll
             for (int c = 0; c < TB_NQ; c++) acs[j][c] = fabs(TB_X(c, TB_P - 1 + j));
+        /* Which of the two candidates (eps/m1)^(1/(P-1)), (eps/m2)^(1/P) is the minimum is decided from single-precision
+         * logarithms (exponent + MUFU.LG2 of the mantissa, absolute error ~1e-6 in log2 h) whenever they differ by more
+         * than 1e-4 in log2 -- tb_pow errs by < 1 ulp, so the order of the two double-double powers cannot differ -- and
+         * only that one is evaluated: one ~300-instruction tb_pow per step instead of two, same bits.                */
+        int skip_k = -1;
+#if !TB_STEPSIZE_PAIR
+        {
+            double mm[2] = {0.0, 0.0};
+#pragma unroll
+            for (int j = 0; j < 2; j++)
+#pragma unroll
+                for (int c = 0; c < TB_NQ; c++) mm[j] = fmax(mm[j], acs[j][c]);
+            if (mm[0] > 0.0 && mm[1] > 0.0 && mm[0] < TB_INF && mm[1] < TB_INF && a.abstol > 0.0) {
+                float l2[3];
+                const double v[3] = {a.abstol, mm[0], mm[1]};
+#pragma unroll
+                for (int j = 0; j < 3; j++) {
+                    const int hi = __double2hiint(v[j]);
+                    const int ex = ((hi >> 20) & 0x7ff) - 1023; /* subnormals land far off: harmless, only a hint */
+                    const double mant = __hiloint2double((hi & 0x000fffff) | 0x3ff00000, __double2loint(v[j]));
+                    l2[j] = (float)ex + __log2f((float)mant);
+                }
+                const float e1 = (l2[0] - l2[1]) * (1.0f / (float)(TB_P - 1)), e2 = (l2[0] - l2[2]) * (1.0f / (float)TB_P);
+                /* eps/m must be a normal number as well: a subnormal (or zero) quotient is not what the logarithms describe */
+                const bool normal = fabsf(l2[0] - l2[1]) < 1000.0f && fabsf(l2[0] - l2[2]) < 1000.0f &&
+                                    ((__double2hiint(mm[0]) >> 20) & 0x7ff) != 0 && ((__double2hiint(mm[1]) >> 20) & 0x7ff) != 0 &&
+                                    ((__double2hiint(a.abstol) >> 20) & 0x7ff) != 0;
+                if (normal && e1 - e2 > 1e-4f) skip_k = TB_P - 1;      /* the k = P candidate is the smaller one */
+                else if (normal && e2 - e1 > 1e-4f) skip_k = TB_P;
+            }
+        }
+#endif
 #pragma unroll
         for (int k = TB_P - 1; k <= TB_P; k++) {
             double m = 0.0, ac[TB_NQ];
 #pragma unroll
             for (int c = 0; c < TB_NQ; c++) { ac[c] = acs[k - (TB_P - 1)][c]; m = fmax(m, ac[c]); anynan = anynan || (ac[c] != ac[c]); }
-            if (m != 0.0) {
+            if (m != 0.0 && k != skip_k) {
 #if TB_STEPSIZE_PAIR
                 double hk = both ? (k == TB_P ? hp.b : hp.a) : tb_stepsize_k(m, a.abstol, k);
 #else
@@ -763,6 +795,7 @@ extern "C" __global__ void __launch_bounds__(TB_BT, TB_MINB) tb_ensemble_kernel(
                     long long i = (long long)base + lane;
                     if (i < a.N) {
                         have = true;
+                        if (a.queue_reverse) i = a.N - 1 - i;
                         if (tb_traj_init(T, smt, a, i)) { tb_traj_finish(T, a); have = false; }
                     }
                 }
@@ -772,6 +805,9 @@ extern "C" __global__ void __launch_bounds__(TB_BT, TB_MINB) tb_ensemble_kernel(
                 long long i = (long long)atomicAdd(a.counter, 1ull);
                 if (i >= a.N) { more = false; break; }
                 have = true;
+                /* a lane that refills near the end of the queue runs alone while the others idle: when the caller
+                 * says the cost grows with the index, the expensive trajectories are handed out first            */
+                if (a.queue_reverse) i = a.N - 1 - i;
                 if (tb_traj_init(T, smt, a, i)) { tb_traj_finish(T, a); have = false; }
             }
         }
@@ -990,6 +1026,7 @@ extern "C" __global__ void __launch_bounds__(TB_BT, TB_MINB) tb_ensemble_kernel(
             i = __shfl_sync(T.tmask, i, T.leader);
             if (i >= a.N) { more = false; break; }
             have = true;
+            if (a.queue_reverse) i = a.N - 1 - i;
             if (tb_traj_init(T, smt, a, i)) { tb_traj_finish(T, a); have = false; }
         }
 #if TB_BAR == 2

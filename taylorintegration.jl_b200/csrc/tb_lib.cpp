@@ -99,7 +99,7 @@ struct TbArgs {
     int params_per_traj;
     int eventorder, newtoniter, event_cap;
     int lockstep;
-    int pad0;
+    int queue_reverse;
     double *xfinal;
     double *tfinal;
     long long *nsteps;
@@ -280,6 +280,7 @@ static void fill_args(TbArgs &a, int64_t N, const double *q0, const double *para
     a.newtoniter = o.newtoniter;
     a.event_cap = o.event_capacity > 0 ? o.event_capacity : (int)(o.maxsteps + 1);
     a.lockstep = (out.tv || out.xv || out.psol || out.lambda_v) ? 1 : 0;
+    a.queue_reverse = o.sort_by_cost == 1 ? 1 : 0;
     a.xfinal = out.xfinal;
     a.tfinal = out.tfinal;
     a.nsteps = (long long *)out.nsteps;

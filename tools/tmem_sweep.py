@@ -41,6 +41,8 @@ if cfg_file:
     configs = [(c["name"], c["kw"]) for c in json.load(open(cfg_file))]
 for mode in modes:
     for name, kw in configs:
+        kw = dict(kw)
+        opts.sort_by_cost = int(kw.pop("sort_by_cost", 0))
         try:
             k = tb.Kernel(tape, 28, L.KIND_PLAIN, mode, **kw)
         except Exception as e:
