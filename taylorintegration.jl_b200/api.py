@@ -322,6 +322,8 @@ def _integrate(tape: Tape, kind: int, q0, t0, tmax, trange, order, abstol, param
     if output not in ("steps", "final"):
         raise ValueError("output must be 'steps' or 'final'")
     kernel_opts = dict(kernel_opts or {})
+    # scheduling hint (tb_opts_t.sort_by_cost): 1 = the ensemble's cost grows with the index, hand out the far end first
+    sort_by_cost = int(kernel_opts.pop("sort_by_cost", 0))
     wide = bool(kernel_opts.pop("wide", False)) or is_wide(tape)
     kkind = kind
     if wide:
@@ -347,7 +349,8 @@ def _integrate(tape: Tape, kind: int, q0, t0, tmax, trange, order, abstol, param
             kernel_opts["flags"] = int(kernel_opts.get("flags", 0)) | 262144
         k = get_kernel(ktape, int(order), kkind, _mode(mode), **(kernel_opts or {}))
     cap = int(event_capacity) if event_capacity else int(maxsteps) + 1
-    o = make_opts(abstol, reltol, minstepsize, maxstepsize, maxsteps, eventorder, newtoniter, nrabstol, cap, per)
+    o = make_opts(abstol, reltol, minstepsize, maxstepsize, maxsteps, eventorder, newtoniter, nrabstol, cap, per,
+                  sort_by_cost=sort_by_cost)
     stride = int(maxsteps) + 1
     out = L.TbOut()
     xfinal, tfinal = np.empty((dof, N)), np.empty(N)
