@@ -375,6 +375,13 @@ int tb_wide_info(const tb_wide_t *w, int *nops, int *nlev, int *nser, int *maxwi
  * carries its own).  TB_ERR_UNSUPPORTED when the stored series do not fit (the global-workspace kernel runs then). */
 int tb_wide_layout(const tb_wide_t *w, int *nclusters, int *npersistent, int *ntransient, int *threads, int *smem_bytes,
                    int *ctas_per_sm, int *ngroups);
+/* The cluster kernel is specialised per program by NVRTC when its clusters form groups: the group programs become
+ * straight-line code with compile-time entries (no dispatch, unrolled coupling sums, the head of each coupling sum's
+ * constants in registers).  generated = 0: the interpreter of libtaylorb200.so runs.  tb_wide_source / tb_wide_log:
+ * the generated text and the NVRTC / ptxas log. */
+int tb_wide_generated(const tb_wide_t *w, int *generated, int *regs, int *local_bytes, int *lc_in_smem);
+const char *tb_wide_source(const tb_wide_t *w);
+const char *tb_wide_log(const tb_wide_t *w);
 int tb_wide_integrate(tb_wide_t *w, int64_t N, const double *q0, const double *params, double t0, double tmax,
                       const double *trange, int64_t nt, const tb_opts_t *opts, const tb_out_t *out);
 

@@ -87,7 +87,7 @@ class TbOut(C.Structure):
 
 EXPORTS = [
     "tb_abi_version", "tb_last_error", "tb_ode_create", "tb_ode_free", "tb_opts_default", "tb_compile_opts_default",
-    "tb_generate_source", "tb_compile", "tb_integrate_multi", "tb_wide_layout", "tb_dense_eval_device", "tb_serialize_device", "tb_kernel_free", "tb_kernel_source", "tb_kernel_log", "tb_kernel_info",
+    "tb_generate_source", "tb_compile", "tb_integrate_multi", "tb_wide_layout", "tb_wide_generated", "tb_wide_source", "tb_wide_log", "tb_dense_eval_device", "tb_serialize_device", "tb_kernel_free", "tb_kernel_source", "tb_kernel_log", "tb_kernel_info",
     "tb_kernel_cubin", "tb_integrate", "tb_integrate_trange", "tb_work_bytes", "tb_integrate_device",
     "tb_launch_count", "tb_jet", "tb_dense_eval", "tb_fp64_peak", "tb_device_count", "tb_set_device",
     "tb_tn_create", "tb_tn_free", "tb_tn_ncoef", "tb_tn_monomials", "tb_tn_integrate",
@@ -164,6 +164,9 @@ def lib() -> C.CDLL:
     L.tb_wide_free.argtypes = [vp]
     L.tb_wide_info.argtypes = [vp] + [C.POINTER(C.c_int)] * 4
     L.tb_wide_layout.argtypes = [vp] + [C.POINTER(C.c_int)] * 7
+    L.tb_wide_generated.argtypes = [vp] + [C.POINTER(C.c_int)] * 4
+    L.tb_wide_source.argtypes = [vp]; L.tb_wide_source.restype = C.c_char_p
+    L.tb_wide_log.argtypes = [vp]; L.tb_wide_log.restype = C.c_char_p
     L.tb_wide_integrate.argtypes = [vp, C.c_int64, vp, vp, C.c_double, C.c_double, vp, C.c_int64, C.POINTER(TbOpts),
                                     C.POINTER(TbOut)]
     _lib = L

@@ -139,7 +139,21 @@ class WideKernel:
         if L.lib().tb_wide_layout(self._w, *[C.byref(x) for x in v2]) == 0:  # the shared-memory cluster kernel applies
             d.update(zip(["clusters", "stored_series", "scalar_slots", "threads", "smem_bytes", "ctas_per_sm", "groups"],
                          [x.value for x in v2]))
+            v3 = [C.c_int(0) for _ in range(4)]
+            if L.lib().tb_wide_generated(self._w, *[C.byref(x) for x in v3]) == 0:
+                d.update(zip(["generated", "regs", "local_bytes", "coupling_in_smem"], [x.value for x in v3]))
         return d
+
+    @property
+    def source(self) -> str:
+        """Text of the NVRTC-specialised cluster kernel ('' when the interpreter runs)."""
+        s = L.lib().tb_wide_source(self._w)
+        return s.decode() if s else ""
+
+    @property
+    def log(self) -> str:
+        s = L.lib().tb_wide_log(self._w)
+        return s.decode() if s else ""
 
 
 def is_wide(tape: Tape) -> bool:

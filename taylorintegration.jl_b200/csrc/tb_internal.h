@@ -40,6 +40,12 @@ const char *embedded_device_pre();
 const char *embedded_device_drv();
 
 void set_error(const std::string &msg);
+/* NVRTC -> sm_100a cubin with the in-tree disk cache (tb_lib.cpp); module / launch helpers over the driver API */
+int compile_cubin(const std::string &source, int mode, bool disk_cache, std::vector<char> &cubin, std::string &log);
+int module_load(const std::vector<char> &cubin, const char *fname, size_t smem, void **mod, void **fn);
+void module_unload(void *mod);
+int launch_fn(void *fn, unsigned grid, unsigned block, size_t smem, void *stream, void *arg_struct);
+const char *embedded_wide2_dev();
 void set_last_kernel_ms(double ms);
 
 } // namespace tb

@@ -598,6 +598,97 @@ static std::string cache_path(const std::string &source, int mode) {
     return dir + name;
 }
 
+/* NVRTC -> cubin for sm_100a with the in-tree disk cache; shared by the ensemble kernels (tb_compile) and the generated
+ * cluster kernels of tb_wide2.cu */
+} // extern "C"
+namespace tb {
+int compile_cubin(const std::string &source, int mode, bool disk_cache, std::vector<char> &cubin, std::string &log) {
+    /* on-disk cubin cache (in-tree, next to the library, so build() on the CPU box pre-compiles for the GPU box):
+     * key = FNV-1a of the generated source + compile mode.  TB_CF_NO_DISK_CACHE skips it. */
+    const std::string cpath = disk_cache ? cache_path(source, mode) : std::string();
+    if (!cpath.empty() && read_file(cpath + ".cubin", cubin) && !cubin.empty()) {
+        std::vector<char> lg;
+        if (read_file(cpath + ".log", lg)) log.assign(lg.begin(), lg.end());
+        /* a cubin written by an OLDER NVRTC than the one running is stale (toolkit upgrade): recompile.  One written
+         * by a newer NVRTC is kept: that is build()'s CUDA 12.9 cubin met by a process whose libnvrtc.so.12 resolved
+         * to torch's bundled 12.8, whose ptxas spills where 12.9 does not.                                         */
+        int cmaj = 0, cmin = 0, rmaj = 0, rmin = 0;
+        const size_t vp = log.rfind("compiled by NVRTC ");
+        const bool stamped = vp != std::string::npos && sscanf(log.c_str() + vp, "compiled by NVRTC %d.%d", &cmaj, &cmin) == 2;
+        nvrtcVersion(&rmaj, &rmin);
+        if (stamped && (rmaj < cmaj || (rmaj == cmaj && rmin <= cmin))) {
+            return TB_OK;
+        }
+        cubin.clear();
+        log.clear();
+    }
+    nvrtcProgram prog;
+    if (nvrtcCreateProgram(&prog, source.c_str(), "tb_kernel.cu", 0, nullptr, nullptr) != NVRTC_SUCCESS) {
+        set_error("nvrtcCreateProgram failed");
+        return TB_ERR_COMPILE;
+    }
+    std::vector<const char *> o = {"--gpu-architecture=sm_100a", "-std=c++17", "-lineinfo", "--ptxas-options=-v",
+                                   "-default-device"};
+    o.push_back(mode == TB_MODE_PARITY ? "--fmad=false" : "--fmad=true");
+    o.push_back("--prec-div=true");
+    o.push_back("--prec-sqrt=true");
+    /* experiment hook: extra ptxas options (e.g. TB_PTXAS_EXTRA=-O2), part of the cache key */
+    std::string extra;
+    if (const char *x = getenv("TB_PTXAS_EXTRA")) { extra = std::string("--ptxas-options=") + x; o.push_back(extra.c_str()); }
+    nvrtcResult r = nvrtcCompileProgram(prog, (int)o.size(), o.data());
+    size_t ls = 0;
+    nvrtcGetProgramLogSize(prog, &ls);
+    log.resize(ls);
+    if (ls) nvrtcGetProgramLog(prog, &log[0]);
+    if (r != NVRTC_SUCCESS) {
+        set_error(std::string("NVRTC: ") + nvrtcGetErrorString(r) + "\n" + log);
+        nvrtcDestroyProgram(&prog);
+        return TB_ERR_COMPILE;
+    }
+    size_t cs = 0;
+    nvrtcGetCUBINSize(prog, &cs);
+    cubin.resize(cs);
+    nvrtcGetCUBIN(prog, cubin.data());
+    nvrtcDestroyProgram(&prog);
+    if (!cpath.empty()) {
+        write_file(cpath + ".cubin", cubin.data(), cubin.size());
+        int maj = 0, min = 0;
+        nvrtcVersion(&maj, &min);
+        log += "\n[libtaylorb200] compiled by NVRTC " + std::to_string(maj) + "." + std::to_string(min) + "\n";
+        write_file(cpath + ".log", log.data(), log.size());
+    }
+    return TB_OK;
+}
+int module_load(const std::vector<char> &cubin, const char *fname, size_t smem, void **mod, void **fn) {
+    Driver &d = driver();
+    if (!d.ok) { set_error(d.why); return TB_ERR_CUDA; }
+    TB_CUDA(cudaFree(0)); /* make the primary context current */
+    CUmodule m = nullptr;
+    CUfunction f = nullptr;
+    CUresult r = d.ModuleLoadData(&m, cubin.data());
+    if (r != CUDA_SUCCESS) { set_error("cuModuleLoadData: " + cu_err(r)); return TB_ERR_CUDA; }
+    r = d.ModuleGetFunction(&f, m, fname);
+    if (r != CUDA_SUCCESS) { set_error(std::string("cuModuleGetFunction(") + fname + "): " + cu_err(r)); d.ModuleUnload(m); return TB_ERR_CUDA; }
+    r = d.FuncSetAttribute(f, CU_FUNC_ATTRIBUTE_MAX_DYNAMIC_SHARED_SIZE_BYTES, (int)smem);
+    if (r != CUDA_SUCCESS) { set_error("cuFuncSetAttribute(max dynamic smem): " + cu_err(r)); d.ModuleUnload(m); return TB_ERR_CUDA; }
+    *mod = m;
+    *fn = f;
+    return TB_OK;
+}
+void module_unload(void *mod) {
+    if (mod && driver().ok) driver().ModuleUnload((CUmodule)mod);
+}
+int launch_fn(void *fn, unsigned grid, unsigned block, size_t smem, void *stream, void *arg_struct) {
+    void *params[1] = {arg_struct};
+    CUresult r = driver().LaunchKernel((CUfunction)fn, grid, 1, 1, block, 1, 1, (unsigned)smem, (CUstream)stream, params, nullptr);
+    if (r != CUDA_SUCCESS) { set_error("cuLaunchKernel: " + cu_err(r)); return TB_ERR_CUDA; }
+    count_launch(1);
+    return TB_OK;
+}
+} // namespace tb
+using namespace tb;
+extern "C" {
+
 const char *tb_generate_source(const tb_ode_t *ode, const tb_compile_opts_t *co) {
     static thread_local std::string src;
     if (!ode || !co) { set_error("tb_generate_source: NULL argument"); return nullptr; }
@@ -620,64 +711,11 @@ tb_kernel_t *tb_compile(const tb_ode_t *ode, const tb_compile_opts_t *co) {
         delete k;
         return nullptr;
     }
-    /* on-disk cubin cache (in-tree, next to the library, so build() on the CPU box pre-compiles for the GPU box):
-     * key = FNV-1a of the generated source + compile mode.  TB_CF_NO_DISK_CACHE skips it. */
-    const std::string cpath = (k->co.flags & TB_CF_NO_DISK_CACHE) ? std::string() : cache_path(k->source, k->co.mode);
-    if (!cpath.empty() && read_file(cpath + ".cubin", k->cubin) && !k->cubin.empty()) {
-        std::vector<char> lg;
-        if (read_file(cpath + ".log", lg)) k->log.assign(lg.begin(), lg.end());
-        /* a cubin written by an OLDER NVRTC than the one running is stale (toolkit upgrade): recompile.  One written
-         * by a newer NVRTC is kept: that is build()'s CUDA 12.9 cubin met by a process whose libnvrtc.so.12 resolved
-         * to torch's bundled 12.8, whose ptxas spills where 12.9 does not.                                         */
-        int cmaj = 0, cmin = 0, rmaj = 0, rmin = 0;
-        const size_t vp = k->log.rfind("compiled by NVRTC ");
-        const bool stamped = vp != std::string::npos && sscanf(k->log.c_str() + vp, "compiled by NVRTC %d.%d", &cmaj, &cmin) == 2;
-        nvrtcVersion(&rmaj, &rmin);
-        if (stamped && (rmaj < cmaj || (rmaj == cmaj && rmin <= cmin))) {
-            parse_ptxas(k->log, &k->regs, &k->local_bytes);
-            return k;
-        }
-        k->cubin.clear();
-        k->log.clear();
-    }
-    nvrtcProgram prog;
-    if (nvrtcCreateProgram(&prog, k->source.c_str(), "tb_kernel.cu", 0, nullptr, nullptr) != NVRTC_SUCCESS) {
-        set_error("nvrtcCreateProgram failed");
+    if (compile_cubin(k->source, k->co.mode, !(k->co.flags & TB_CF_NO_DISK_CACHE), k->cubin, k->log) != TB_OK) {
         delete k;
         return nullptr;
     }
-    std::vector<const char *> o = {"--gpu-architecture=sm_100a", "-std=c++17", "-lineinfo", "--ptxas-options=-v",
-                                   "-default-device"};
-    o.push_back(k->co.mode == TB_MODE_PARITY ? "--fmad=false" : "--fmad=true");
-    o.push_back("--prec-div=true");
-    o.push_back("--prec-sqrt=true");
-    /* experiment hook: extra ptxas options (e.g. TB_PTXAS_EXTRA=-O2), part of the cache key */
-    std::string extra;
-    if (const char *x = getenv("TB_PTXAS_EXTRA")) { extra = std::string("--ptxas-options=") + x; o.push_back(extra.c_str()); }
-    nvrtcResult r = nvrtcCompileProgram(prog, (int)o.size(), o.data());
-    size_t ls = 0;
-    nvrtcGetProgramLogSize(prog, &ls);
-    k->log.resize(ls);
-    if (ls) nvrtcGetProgramLog(prog, &k->log[0]);
-    if (r != NVRTC_SUCCESS) {
-        set_error(std::string("NVRTC: ") + nvrtcGetErrorString(r) + "\n" + k->log);
-        nvrtcDestroyProgram(&prog);
-        delete k;
-        return nullptr;
-    }
-    size_t cs = 0;
-    nvrtcGetCUBINSize(prog, &cs);
-    k->cubin.resize(cs);
-    nvrtcGetCUBIN(prog, k->cubin.data());
-    nvrtcDestroyProgram(&prog);
     parse_ptxas(k->log, &k->regs, &k->local_bytes);
-    if (!cpath.empty()) {
-        write_file(cpath + ".cubin", k->cubin.data(), k->cubin.size());
-        int maj = 0, min = 0;
-        nvrtcVersion(&maj, &min);
-        k->log += "\n[libtaylorb200] compiled by NVRTC " + std::to_string(maj) + "." + std::to_string(min) + "\n";
-        write_file(cpath + ".log", k->log.data(), k->log.size());
-    }
     return k;
 }
 

@@ -551,6 +551,17 @@ int tb_wide_layout(const tb_wide_t *w, int *nclusters, int *npersistent, int *nt
     return TB_OK;
 }
 
+/* the NVRTC-specialised build of the cluster kernel: 1 / registers / stack bytes / coupling constants in shared memory,
+ * or generated = 0 when the interpreter runs (no groups of isomorphic clusters, or TB_WIDE_INTERP=1) */
+int tb_wide_generated(const tb_wide_t *w, int *generated, int *regs, int *local_bytes, int *lc_in_smem) {
+    if (!w) return TB_ERR_ARG;
+    if (!w->v2) { tb::set_error("tb_wide_generated: " + w->v2_why); return TB_ERR_UNSUPPORTED; }
+    tbw::wide2_gen_info(w->v2, generated, regs, local_bytes, lc_in_smem);
+    return TB_OK;
+}
+const char *tb_wide_source(const tb_wide_t *w) { return (w && w->v2) ? tbw::wide2_gen_source(w->v2) : nullptr; }
+const char *tb_wide_log(const tb_wide_t *w) { return (w && w->v2) ? tbw::wide2_gen_log(w->v2) : nullptr; }
+
 int tb_wide_integrate(tb_wide_t *w, int64_t N, const double *q0, const double *params, double t0, double tmax,
                       const double *trange, int64_t nt, const tb_opts_t *o, const tb_out_t *out) {
     if (!w || !q0 || !o || !out || N < 0 || (trange && nt < 2)) { tb::set_error("tb_wide_integrate: bad argument"); return TB_ERR_ARG; }

@@ -54,419 +54,8 @@ namespace tbw {
         }                                                                      \
     } while (0)
 
-/* location of a series: >= 0 persistent id (shared memory W[k*NS + id]); -1 a number; <= -2 transient slot -2 - loc */
-struct C2Op {
-    int op, res, a, b, aux;
-    int flags; /* bit 0: operand a enters negated, bit 1: operand b */
-    int para, parb;
-    int lc_off, lc_n, lc_stride, lc_soff, lc_sstride;
-    int pad;
-    double imma, immb, imm;
-};
+#include "tb_wide2_dev.cuh"
 
-struct W2Args {
-    long long N;
-    int dof, npar, P, NS, ncl, maxlen, ntr, tsid;
-    const C2Op *ops; /* [maxlen x ncl], op-major */
-    const double *lc_coef;
-    const int *lc_ser;
-    const int *xsid; /* [dof] persistent id of x[c] */
-    const int *cl_len; /* [ncl] entries of cluster c (0: a padding slot) */
-    int lc_smem, lc_count; /* coupling constants copied to shared memory (lc_count doubles) */
-    int ngroups;           /* > 0: group programs */
-    int g_smem, ngops, ngnum; /* group programs copied to shared memory */
-    int g_first[8], g_count[8], g_off[8], g_len[8];
-    const C2Op *gops;
-    const double *gnum;
-    const double *q0, *params, *trange;
-    long long nt;
-    double t0, tmax, abstol, reltol, minstep, maxstep;
-    long long maxsteps;
-    int params_per_traj;
-    double *xfinal, *tfinal;
-    long long *nsteps;
-    int *status;
-    double *xv_trange;
-    unsigned long long *counter;
-};
-
-#define XM(a, b) __dmul_rn((a), (b))
-#define XA(a, b) __dadd_rn((a), (b))
-#define XS(a, b) __dsub_rn((a), (b))
-#define XD(a, b) __ddiv_rn((a), (b))
-template <bool FAST> __device__ __forceinline__ double mad2(double a, double b, double c) {
-    return FAST ? fma(a, b, c) : __dadd_rn(c, __dmul_rn(a, b));
-}
-
-/* one entry of a cluster at order k: the recurrences of SURVEY App. B in the oracle's order (as tb_wide.cu exec_op) */
-template <bool FAST>
-__device__ __forceinline__ void exec2(const W2Args &A, double *__restrict__ W, double *__restrict__ tr, const double *par,
-                                      const double *__restrict__ lcc, const bool lc_smem, const C2Op &o, const int k) {
-    const int NS = A.NS;
-    const bool sa = o.a == -1, sb = o.b == -1;
-    const double na = o.para >= 0 ? par[o.para] : o.imma, nb = o.parb >= 0 ? par[o.parb] : o.immb;
-    /* value of operand series `loc` at index j (transients exist at j == k only) */
-    auto rd = [&](int loc, int j) -> double { return loc >= 0 ? W[j * NS + loc] : tr[(-2 - loc) * blockDim.x]; };
-    int op = o.op;
-    if (op == TB_OP_POW) {
-        if (o.imm == 0.0) op = TB_OP_ONE;
-        else if (o.imm == 1.0) op = TB_OP_IDENTITY;
-        else if (o.imm == 2.0) op = TB_OP_SQR;
-        else if (o.imm == 0.5) op = TB_OP_SQRT;
-    }
-    double r = 0.0;
-    switch (op) {
-        case W_NOP: return;
-        case W_SOLCOEFF: /* x[k+1] = dx[k] / (k+1): TaylorIntegration.jl:33-40 */
-            W[(k + 1) * NS + o.res] = FAST ? rd(o.a, k) * (1.0 / (double)(k + 1)) : XD(rd(o.a, k), (double)(k + 1));
-            return;
-        case TB_OP_IDENTITY: r = sa ? (k == 0 ? na : 0.0) : rd(o.a, k); break;
-        case TB_OP_NEG: r = -rd(o.a, k); break;
-        case TB_OP_ZERO: r = 0.0; break;
-        case TB_OP_ONE: r = k == 0 ? 1.0 : 0.0; break;
-        case TB_OP_ADD:
-            if (sa && sb) r = k == 0 ? XA(na, nb) : 0.0;
-            else if (sa) r = k == 0 ? XA(na, rd(o.b, 0)) : rd(o.b, k);
-            else if (sb) r = k == 0 ? XA(rd(o.a, 0), nb) : rd(o.a, k);
-            else r = XA(rd(o.a, k), rd(o.b, k));
-            break;
-        case TB_OP_SUB:
-            if (sa && sb) r = k == 0 ? XS(na, nb) : 0.0;
-            else if (sa) r = k == 0 ? XS(na, rd(o.b, 0)) : -rd(o.b, k);
-            else if (sb) r = k == 0 ? XS(rd(o.a, 0), nb) : rd(o.a, k);
-            else r = XS(rd(o.a, k), rd(o.b, k));
-            break;
-        case TB_OP_MUL:
-            if (sa && sb) r = k == 0 ? XM(na, nb) : 0.0;
-            else if (sa) r = XM(na, rd(o.b, k));
-            else if (sb) r = XM(rd(o.a, k), nb);
-            else { /* Cauchy product; a negated operand is negated on the fly (exact: a sign bit on the DMUL operand) */
-                const double *pa = W + o.a, *pb = W + o.b + k * NS;
-                const bool neg = ((o.flags & 1) != 0) != ((o.flags & 2) != 0);
-                r = XM(neg ? -pa[0] : pa[0], pb[0]);
-                if (FAST) {
-                    for (int i = 1; i <= k; i++) { pa += NS; pb -= NS; r = fma(neg ? -pa[0] : pa[0], pb[0], r); }
-                } else {
-                    int i = 1;
-                    for (; i + 2 <= k + 1; i += 2) { /* two products ahead of the dependent adds */
-                        const double q0 = XM(pa[NS], pb[-NS]), q1 = XM(pa[2 * NS], pb[-2 * NS]);
-                        pa += 2 * NS; pb -= 2 * NS;
-                        r = XA(r, neg ? -q0 : q0); r = XA(r, neg ? -q1 : q1);
-                    }
-                    for (; i <= k; i++) { pa += NS; pb -= NS; const double q = XM(pa[0], pb[0]); r = XA(r, neg ? -q : q); }
-                }
-            }
-            break;
-        case TB_OP_SQR: {
-            const double *a = W + o.a;
-            if (k == 0) r = XM(a[0], a[0]);
-            else {
-                const int kodd = k & 1, kend = (k - 2 + kodd) / 2;
-                r = XM(a[0], a[k * NS]);
-                for (int i = 1; i <= kend; i++) r = mad2<FAST>(a[i * NS], a[(k - i) * NS], r);
-                r = XM(2.0, r);
-                if (!kodd) r = mad2<FAST>(a[(k / 2) * NS], a[(k / 2) * NS], r);
-            }
-            break;
-        }
-        case TB_OP_DIV:
-            if (sa && sb) r = k == 0 ? XD(na, nb) : 0.0;
-            else if (sb) r = XD(rd(o.a, k), nb);
-            else if (k == 0) r = XD(sa ? na : rd(o.a, 0), W[o.b]);
-            else {
-                const double *b = W + o.b, *c = W + o.res;
-                double s = XM(c[0], b[k * NS]);
-                for (int i = 1; i <= k - 1; i++) s = mad2<FAST>(c[i * NS], b[(k - i) * NS], s);
-                r = sa ? XD(-s, b[0]) : XD(XS(rd(o.a, k), s), b[0]);
-            }
-            break;
-        case TB_OP_SQRT: {
-            const double *c = W + o.res;
-            if (k == 0) r = __dsqrt_rn(rd(o.a, 0));
-            else {
-                const int kodd = k & 1, kend = (k - 2 + kodd) / 2;
-                double s = 0.0;
-                for (int i = 1; i <= kend; i++) s = i == 1 ? XM(c[i * NS], c[(k - i) * NS]) : mad2<FAST>(c[i * NS], c[(k - i) * NS], s);
-                double aux = XS(rd(o.a, k), XM(2.0, s));
-                if (!kodd) aux = XS(aux, XM(c[(kend + 1) * NS], c[(kend + 1) * NS]));
-                r = XD(aux, XM(2.0, c[0]));
-            }
-            break;
-        }
-        case TB_OP_POW: {
-            const double *a = W + o.a, *c = W + o.res;
-            if (k == 0) r = tb_pow(a[0], o.imm);
-            else {
-                double s = XM(XM(XM(o.imm, (double)k), c[0]), a[k * NS]);
-                for (int i = 1; i <= k - 1; i++) {
-                    const double rr = XS(XM(o.imm, (double)(k - i)), (double)i);
-                    s = mad2<FAST>(XM(rr, c[i * NS]), a[(k - i) * NS], s);
-                }
-                r = XD(s, XM((double)k, a[0]));
-            }
-            break;
-        }
-        case TB_OP_EXP: {
-            const double *a = W + o.a, *c = W + o.res;
-            if (k == 0) r = tb_exp(a[0]);
-            else {
-                double s = XM(XM((double)k, a[k * NS]), c[0]);
-                for (int i = 1; i <= k - 1; i++) s = mad2<FAST>(XM((double)(k - i), a[(k - i) * NS]), c[i * NS], s);
-                r = XD(s, (double)k);
-            }
-            break;
-        }
-        case TB_OP_LOG: {
-            const double *a = W + o.a, *c = W + o.res;
-            if (k == 0) r = tb_log(a[0]);
-            else if (k == 1) r = XD(a[NS], a[0]);
-            else {
-                double s = XM(XM((double)(k - 1), a[NS]), c[(k - 1) * NS]);
-                for (int i = 2; i <= k - 1; i++) s = mad2<FAST>(XM((double)(k - i), a[i * NS]), c[(k - i) * NS], s);
-                r = XD(XS(a[k * NS], XD(s, (double)k)), a[0]);
-            }
-            break;
-        }
-        case TB_OP_SINCOS: {
-            const double *a = W + o.a;
-            double *sn = W + o.res, *cs = W + o.aux;
-            if (k == 0) { double s, c; tb_sincos(a[0], &s, &c); sn[0] = s; cs[0] = c; return; }
-            double x = a[NS];
-            double sk = XM(x, cs[(k - 1) * NS]), ck = XM(-x, sn[(k - 1) * NS]);
-            for (int i = 2; i <= k; i++) {
-                x = XM((double)i, a[i * NS]);
-                sk = mad2<FAST>(x, cs[(k - i) * NS], sk);
-                ck = FAST ? fma(-x, sn[(k - i) * NS], ck) : XS(ck, XM(x, sn[(k - i) * NS]));
-            }
-            sn[k * NS] = XD(sk, (double)k);
-            cs[k * NS] = XD(ck, (double)k);
-            return;
-        }
-        case W_LINCOMB: { /* ((start + c1 x1[k]) + c2 x2[k]) + ... : the fused add!/mul! chain, in tape order */
-            const double *cf = lcc + o.lc_off;
-            const double *Wk = W + k * NS;
-            const int ls = o.lc_stride, n = o.lc_n;
-            int j = 0;
-            if (o.lc_sstride == 0) {
-                /* the terms are consecutive stored series (x_1[k], x_2[k], ...: the state jets of the other clusters):
-                 * no id table, the operand pointer just advances; products are formed one batch ahead of the adds */
-                const double *xs = Wk + o.lc_soff;
-                const int xstep = o.pad;
-                if (sa) { const double m0 = XM(cf[0], xs[0]); r = k == 0 ? XA(na, m0) : m0; j = 1; cf += ls; xs += xstep; }
-                else r = rd(o.a, k);
-                if (FAST) {
-                    for (; j < n; j++, cf += ls, xs += xstep) r = fma(cf[0], xs[0], r);
-                } else {
-                    double p0 = 0.0, p1 = 0.0, p2 = 0.0, p3 = 0.0;
-                    bool have = false;
-                    for (; j + 4 <= n; j += 4) {
-                        const double q0 = XM(cf[0], xs[0]), q1 = XM(cf[ls], xs[xstep]);
-                        const double q2 = XM(cf[2 * ls], xs[2 * xstep]), q3 = XM(cf[3 * ls], xs[3 * xstep]);
-                        cf += 4 * ls; xs += 4 * xstep;
-                        if (have) { r = XA(r, p0); r = XA(r, p1); r = XA(r, p2); r = XA(r, p3); }
-                        p0 = q0; p1 = q1; p2 = q2; p3 = q3; have = true;
-                    }
-                    if (have) { r = XA(r, p0); r = XA(r, p1); r = XA(r, p2); r = XA(r, p3); }
-                    for (; j < n; j++, cf += ls, xs += xstep) r = XA(r, XM(cf[0], xs[0]));
-                }
-            } else {
-                const int *sr = A.lc_ser + o.lc_soff;
-                const int ss = o.lc_sstride;
-                if (sa) { const double m0 = XM(cf[0], Wk[__ldg(sr)]); r = k == 0 ? XA(na, m0) : m0; j = 1; cf += ls; sr += ss; }
-                else r = rd(o.a, k);
-                for (; j < n; j++, cf += ls, sr += ss) r = mad2<FAST>(cf[0], Wk[__ldg(sr)], r);
-            }
-            break;
-        }
-        default: break;
-    }
-    if (o.res >= 0) W[k * NS + o.res] = r;
-    else tr[(-2 - o.res) * blockDim.x] = r;
-}
-
-__device__ __forceinline__ double w2_horner(const double *X, int NS, int P, double dt) {
-    double s = X[P * NS];
-    for (int k = P - 1; k >= 0; k--) s = XA(XM(s, dt), X[k * NS]);
-    return s;
-}
-
-/* block-wide min (or max) that PROPAGATES NaN like Julia's min / max (stepsize.jl:74, 86) */
-__device__ double w2_block_reduce(double v, double *red, bool take_max) {
-    bool nan = v != v;
-    for (int o = 16; o > 0; o >>= 1) {
-        const double u = __shfl_xor_sync(0xffffffffu, v, o);
-        v = take_max ? fmax(v, u) : fmin(v, u);
-    }
-    const int w = threadIdx.x >> 5, nw = (blockDim.x + 31) >> 5;
-    nan = __syncthreads_or(nan);
-    if ((threadIdx.x & 31) == 0) red[w] = v;
-    __syncthreads();
-    double r = red[0];
-    for (int i = 1; i < nw; i++) r = take_max ? fmax(r, red[i]) : fmin(r, red[i]);
-    return nan ? __longlong_as_double(0x7FF8000000000000LL) : r;
-}
-
-template <bool FAST> __global__ void __launch_bounds__(256, 1) wide2_kernel(const W2Args a) {
-    extern __shared__ double sm2[];
-    __shared__ double red[8];
-    __shared__ unsigned long long s_idx;
-    const int tid = threadIdx.x, nth = blockDim.x, P = a.P, NS = a.NS;
-    double *W = sm2;                              /* [P+1][NS] persistent series */
-    double *tr = W + (size_t)(P + 1) * NS + tid;  /* [ntr][nth] transient scalars of the current order */
-    double *xnew = W + (size_t)(P + 1) * NS + (size_t)a.ntr * nth; /* [dof] */
-    const double *lcc = a.lc_coef;
-    double *extra = xnew + a.dof + 8;
-    if (a.lc_smem) { /* loop-invariant coupling constants: once per CTA */
-        for (int j = tid; j < a.lc_count; j += nth) extra[j] = a.lc_coef[j];
-        lcc = extra;
-        extra += a.lc_count;
-    }
-    const C2Op *gops = a.gops;
-    const double *gnum = a.gnum;
-    if (a.g_smem) {
-        double *gn = extra;
-        for (int j = tid; j < a.ngnum; j += nth) gn[j] = a.gnum[j];
-        int *go = (int *)(gn + a.ngnum);
-        const int *src = (const int *)a.gops;
-        for (int j = tid; j < a.ngops * (int)(sizeof(C2Op) / 4); j += nth) go[j] = src[j];
-        gnum = gn;
-        gops = (const C2Op *)go;
-    }
-    __syncthreads();
-    const double inf = __longlong_as_double(0x7FF0000000000000LL), nan = __longlong_as_double(0x7FF8000000000000LL);
-    for (;;) {
-        if (tid == 0) s_idx = atomicAdd(a.counter, 1ull);
-        __syncthreads();
-        const long long i = (long long)s_idx;
-        __syncthreads();
-        if (i >= a.N) break;
-        double par[8];
-        for (int j = 0; j < a.npar && j < 8; j++) par[j] = a.params_per_traj ? a.params[(long long)j * a.N + i] : a.params[j];
-        for (int c = tid; c < a.dof; c += nth) W[a.xsid[c]] = a.q0[(long long)c * a.N + i];
-        if (a.tsid >= 0) for (int k = tid; k <= P; k += nth) W[k * NS + a.tsid] = k == 1 ? 1.0 : 0.0;
-        double t0 = a.trange ? a.trange[0] : a.t0;
-        const double tmax = a.trange ? a.trange[a.nt - 1] : a.tmax;
-        const double sign = copysign(1.0, XS(tmax, t0));
-        long long nsteps = 1, iter = 2;
-        double t1 = a.trange ? a.trange[1] : 0.0;
-        int st = 0;
-        if (a.trange && a.xv_trange)
-            for (int c = tid; c < a.dof; c += nth) {
-                a.xv_trange[((long long)c * a.nt) * a.N + i] = a.q0[(long long)c * a.N + i];
-                for (long long j = 1; j < a.nt; j++) a.xv_trange[((long long)c * a.nt + j) * a.N + i] = nan;
-            }
-        __syncthreads();
-        while (XM(sign, t0) < XM(sign, tmax)) {
-            if (a.tsid >= 0 && tid == 0) W[a.tsid] = t0;
-            __syncthreads();
-            /* jetcoeffs!: for ord = 0:order-1 (parse_eqs.jl:259-264); every cluster in tape order, then ONE barrier */
-            for (int k = 0; k < P; k++) {
-                if (a.ngroups > 0) {
-                    for (int g = 0; g < a.ngroups; g++)
-                        for (int r = tid; r < a.g_count[g]; r += nth)
-                            for (int j = 0; j < a.g_len[g]; j++) {
-                                C2Op o = gops[a.g_off[g] + j]; /* the same entry for every lane: a broadcast from shared memory */
-                                long long no;
-                                memcpy(&no, &o.immb, sizeof no);
-                                const double lit = ((o.a == -1 && o.para < 0) || (o.b == -1 && o.parb < 0)) ? gnum[no + r] : 0.0;
-                                o.imma = lit; o.immb = lit;
-                                if (o.flags & 16) o.res += r;
-                                if (o.flags & 32) o.a += r;
-                                if (o.flags & 64) o.b += r;
-                                if (o.flags & 128) o.aux += r;
-                                o.lc_off += r;
-                                if (o.flags & 256) o.lc_soff += r;
-                                exec2<FAST>(a, W, tr, par, lcc, a.lc_smem != 0, o, k);
-                            }
-                } else
-                for (int c = tid; c < a.ncl; c += nth) {
-                    const int len = __ldg(a.cl_len + c);
-                    for (int j = 0; j < len; j++) exec2<FAST>(a, W, tr, par, lcc, a.lc_smem != 0, a.ops[(size_t)j * a.ncl + c], k);
-                }
-                __syncthreads();
-            }
-            /* stepsize: stepsize.jl:58-99 */
-            double h = inf;
-            for (int c = tid; c < a.dof; c += nth) {
-                const double *X = W + a.xsid[c];
-                const double x0norm = fabs(X[0]);
-                for (int k = P - 1; k <= P; k++) {
-                    const double ak = fabs(X[k * NS]);
-                    if (ak == 0.0) continue;
-                    const double rel = XM(a.reltol, x0norm);
-                    const double eps = a.abstol >= rel ? a.abstol : rel;
-                    const double hk = tb_pow(XD(eps, ak), XD(1.0, (double)k));
-                    h = (h != h || hk != hk) ? nan : fmin(h, hk);
-                }
-            }
-            h = w2_block_reduce(h, red, false);
-            if (h == inf) { /* _second_stepsize: stepsize.jl:119-132, max over components */
-                double h2 = 0.0;
-                for (int c = tid; c < a.dof; c += nth) {
-                    const double *X = W + a.xsid[c];
-                    bool allzero = true;
-                    for (int k = 0; k <= P; k++) if (X[k * NS] != 0.0) { allzero = false; break; }
-                    double hc = inf;
-                    if (!allzero) {
-                        hc = 0.0;
-                        for (int k = 1; k <= P - 2; k++) {
-                            const double ak = fabs(X[k * NS]);
-                            if (ak == 0.0) continue;
-                            const double hk = tb_pow(XD(1.0, ak), XD(1.0, (double)k));
-                            hc = (hc != hc || hk != hk) ? nan : fmax(hc, hk);
-                        }
-                    }
-                    h2 = (h2 != h2 || hc != hc) ? nan : fmax(h2, hc);
-                }
-                h = w2_block_reduce(h2, red, true);
-            }
-            double dt = h < a.minstep ? a.minstep : (h > a.maxstep ? a.maxstep : h);
-            if (dt == 0.0) { st |= TB_ST_ZERO_STEP; break; }
-            const double rem = XS(tmax, t0);
-            const double srem = XM(sign, rem);
-            dt = XM(sign, (dt != dt || srem != srem) ? nan : fmin(dt, srem));
-            bool fin = true;
-            for (int c = tid; c < a.dof; c += nth) {
-                const double s = w2_horner(W + a.xsid[c], NS, P, dt);
-                xnew[c] = s;
-                fin = fin && isfinite(s);
-            }
-            bool done = false;
-            if (a.trange) {
-                const double tnext = XA(t0, dt);
-                while (XM(sign, t1) < XM(sign, tnext)) {
-                    const double d1 = XS(t1, t0);
-                    if (a.xv_trange)
-                        for (int c = tid; c < a.dof; c += nth)
-                            a.xv_trange[((long long)c * a.nt + (iter - 1)) * a.N + i] = w2_horner(W + a.xsid[c], NS, P, d1);
-                    iter += 1;
-                    t1 = a.trange[iter - 1];
-                }
-                if (dt == rem) {
-                    if (a.xv_trange)
-                        for (int c = tid; c < a.dof; c += nth) a.xv_trange[((long long)c * a.nt + (iter - 1)) * a.N + i] = xnew[c];
-                    done = true;
-                }
-                t0 = tnext;
-            } else
-                t0 = XA(t0, dt);
-            __syncthreads();
-            for (int c = tid; c < a.dof; c += nth) W[a.xsid[c]] = xnew[c];
-            if (done) break;
-            nsteps += 1;
-            if (nsteps > a.maxsteps) { st |= TB_ST_MAXSTEPS; break; }
-            if (__syncthreads_or(!fin)) { st |= TB_ST_NONFINITE; break; }
-        }
-        __syncthreads();
-        if (a.xfinal) for (int c = tid; c < a.dof; c += nth) a.xfinal[(long long)c * a.N + i] = W[a.xsid[c]];
-        if (tid == 0) {
-            if (a.tfinal) a.tfinal[i] = t0;
-            if (a.nsteps) a.nsteps[i] = nsteps - 1;
-            if (a.status) a.status[i] = st;
-        }
-        __syncthreads();
-    }
-}
 
 /* ---- host: fused program -> clusters, persistent / transient placement ------------------------------------- */
 struct Wide2 {
@@ -481,6 +70,13 @@ struct Wide2 {
     std::vector<int> g_first, g_count, g_off, g_len;
     C2Op *d_gops = nullptr;
     double *d_gnum = nullptr;
+    /* NVRTC-specialised build of the group programs (wide2_generate); empty cubin: the interpreter runs */
+    std::vector<char> gen_cubin;
+    std::string gen_source, gen_log;
+    size_t gen_smem = 0;
+    int gen_ctas = 1, gen_regs = 0, gen_local = 0;
+    bool gen_lc_smem = false;
+    std::map<int, std::pair<void *, void *>> gen_loaded; /* device -> (module, function) */
     int device = -1;
     C2Op *d_ops = nullptr;
     double *d_lcc = nullptr;
@@ -505,6 +101,8 @@ static bool cauchy_op(const WOp &o, int which /*0 a, 1 b, 2 res, 3 aux*/) {
         default: return false;
     }
 }
+
+static std::string wide2_generate(const Wide2 *w, bool lc_smem, int ctas, int lcb, int lcreg);
 
 Wide2 *wide2_build(const Program &p, std::string &why) {
     const int n = (int)p.ops.size(), nser = p.nser;
@@ -790,7 +388,7 @@ Wide2 *wide2_build(const Program &p, std::string &why) {
     const int threads = threads_pick;
     w->threads = threads;
     w->smem = ((size_t)(p.order + 1) * NS + (size_t)w->ntr * threads + p.dof + 16) * sizeof(double);
-    const size_t smem_max = 227 * 1024;
+    const size_t smem_max = 227 * 1024, smem_base = w->smem;
     /* the coupling constants are loop-invariant (every order of every step of every trajectory reads all of them):
      * they are copied to shared memory once per CTA when they fit beside the jets.  From global memory the dependent
      * add chain waits on L2 (measured on many-spin 100: 9.1e5 steps/s with 2 CTAs per SM and the table in L1/L2).  */
@@ -805,11 +403,137 @@ Wide2 *wide2_build(const Program &p, std::string &why) {
     if (w->g_smem) w->smem += w->gops.size() * sizeof(C2Op) + w->gnum.size() * sizeof(double);
     if (w->smem > smem_max) { why = "stored series do not fit shared memory (" + std::to_string(w->smem) + " B)"; delete w; return nullptr; }
     w->ctas = (int)std::max<size_t>(1, std::min<size_t>(smem_max / (w->smem + 1024), 2048 / threads));
+    /* NVRTC specialisation of the group programs (TB_WIDE_INTERP=1 keeps the interpreter) */
+    if (!w->gops.empty() && w->gops.size() <= 512 && !getenv("TB_WIDE_INTERP")) {
+        const size_t lcb = w->lc_coef.size() * sizeof(double), gnb = w->gnum.size() * sizeof(double);
+        auto ctas_for = [&](size_t bytes) { return (int)std::max<size_t>(1, std::min<size_t>(smem_max / (bytes + 1024), 2048 / threads)); };
+        /* coupling constants in shared memory only when that does not cost a resident CTA: measured on many-spin 100
+         * (2^14 members), 2 CTAs per SM with the constants through L1/L2 (the head of each sum in registers) 5.5e6
+         * steps/s, 1 CTA per SM with all of them in shared memory 3.2e6 (one warp per scheduler: every latency is
+         * exposed).  TB_WIDE_LC_SMEM=1 / TB_WIDE_LC_GLOBAL=1 force either placement.                                */
+        w->gen_lc_smem = lcb > 0 && smem_base + lcb + gnb + 1024 <= smem_max &&
+                         (ctas_for(smem_base + lcb + gnb) == ctas_for(smem_base + gnb) || getenv("TB_WIDE_LC_SMEM")) && !getenv("TB_WIDE_LC_GLOBAL");
+        w->gen_smem = smem_base + (w->gen_lc_smem ? lcb : 0) + gnb;
+        w->gen_ctas = ctas_for(w->gen_smem);
+        if (const char *e = getenv("TB_WIDE_CTAS")) w->gen_ctas = std::max(1, std::min(w->gen_ctas, atoi(e)));
+        int batch = w->gen_lc_smem ? 6 : 16;
+        if (const char *e = getenv("TB_WIDE_LCB")) batch = std::max(1, std::min(32, atoi(e)));
+        /* doubles of coupling constants per thread held in registers for the whole launch (measured on many-spin 100:
+         * 0 -> 4.28e6, 24 -> 4.76e6, 44 -> 5.48e6, 56 -> 5.58e6, 64 -> 5.64e6 steps/s; 234 registers at 64) */
+        int lcreg = w->gen_lc_smem ? 0 : 60;
+        if (const char *e = getenv("TB_WIDE_LCREG")) lcreg = std::max(0, std::min(100, atoi(e)));
+        w->gen_source = wide2_generate(w, w->gen_lc_smem, w->gen_ctas, batch, lcreg);
+        if (tb::compile_cubin(w->gen_source, w->mode, !getenv("TB_WIDE_NO_CACHE"), w->gen_cubin, w->gen_log) != TB_OK) {
+            if (getenv("TB_WIDE_DEBUG")) fprintf(stderr, "wide2: NVRTC specialisation failed, interpreter kept:\n%s\n", w->gen_log.c_str());
+            w->gen_cubin.clear();
+        } else {
+            const size_t u = w->gen_log.find("Used ");
+            if (u != std::string::npos) sscanf(w->gen_log.c_str() + u, "Used %d registers", &w->gen_regs);
+            const size_t f = w->gen_log.find(" bytes stack frame");
+            if (f != std::string::npos) {
+                size_t b = f;
+                while (b > 0 && isdigit((unsigned char)w->gen_log[b - 1])) b--;
+                w->gen_local = atoi(w->gen_log.c_str() + b);
+            }
+        }
+    }
     return w;
+}
+
+/* ---- NVRTC specialisation ------------------------------------------------------------------------------------
+ * ncu of the interpreter (profiles/r02_ncu_wide2_summary.txt): 84 % of the executed instructions are dispatch and
+ * operand arithmetic, 16 % FP64.  With the group programs emitted as straight-line exec2 calls whose entries are
+ * compile-time constants the switch, the flag tests and the address arithmetic fold away, the coupling sum is
+ * unrolled with its length known, and NS / P / the thread count are literals.  Same device text (tb_wide2_dev.cuh),
+ * same operation order: bit-identical to the interpreter and to the oracle in parity mode.                       */
+static std::string wide2_generate(const Wide2 *w, bool lc_smem, int ctas, int lcb, int lcreg) {
+    std::string s;
+    char buf[1024];
+    auto line = [&](const char *fmt, auto... args) { snprintf(buf, sizeof buf, fmt, args...); s += buf; s += '\n'; };
+    line("/* generated by libtaylorb200 (tb_wide2.cu, wide2_generate): cluster kernel, order %d, %d stored series, %d clusters */",
+         w->order, w->NS, w->ncl);
+    line("#define TB_W2_GENERATED %d", 1);
+    line("#define TB_W2_NS %d", w->NS);
+    line("#define TB_W2_P %d", w->order);
+    line("#define TB_W2_THREADS %d", w->threads);
+    line("#define TB_W2_LCB %d", lcb);
+    line("#define TB_W2_LC_SMEM %d", lc_smem ? 1 : 0);
+    /* register cache of coupling constants: short sums first (their single load would sit on the critical path of
+     * every order), then the head of the long ones, `lcreg` doubles per thread in all */
+    struct Cached { size_t g; int j, n, off; };
+    std::vector<Cached> cached;
+    {
+        int left = lcreg;
+        for (int pass = 0; pass < 2 && left > 0; pass++)
+            for (size_t g = 0; g < w->g_count.size() && left > 0; g++)
+                for (int j = 0; j < w->g_len[g] && left > 0; j++) {
+                    const C2Op &o = w->gops[w->g_off[g] + j];
+                    if (o.op != W_LINCOMB || o.lc_sstride != 0 || o.lc_n <= 0) continue;
+                    if ((pass == 0) != (o.lc_n <= 4)) continue;
+                    const int n = std::min(o.lc_n, left);
+                    cached.push_back({g, j, n, lcreg - left});
+                    left -= n;
+                }
+        lcreg -= left;
+    }
+    auto find_cached = [&](size_t g, int j) -> const Cached * { for (auto &c : cached) if (c.g == g && c.j == j) return &c; return nullptr; };
+    line("#define TB_W2_LCREG %d", lcreg);
+    s += "enum {";
+    const std::pair<const char *, int> ops[] = {
+        {"TB_OP_NOP", TB_OP_NOP}, {"TB_OP_IDENTITY", TB_OP_IDENTITY}, {"TB_OP_NEG", TB_OP_NEG}, {"TB_OP_ADD", TB_OP_ADD},
+        {"TB_OP_SUB", TB_OP_SUB}, {"TB_OP_MUL", TB_OP_MUL}, {"TB_OP_DIV", TB_OP_DIV}, {"TB_OP_SQR", TB_OP_SQR},
+        {"TB_OP_SQRT", TB_OP_SQRT}, {"TB_OP_POW", TB_OP_POW}, {"TB_OP_EXP", TB_OP_EXP}, {"TB_OP_LOG", TB_OP_LOG},
+        {"TB_OP_SINCOS", TB_OP_SINCOS}, {"TB_OP_ZERO", TB_OP_ZERO}, {"TB_OP_ONE", TB_OP_ONE}, {"W_NOP", W_NOP},
+        {"W_LINCOMB", W_LINCOMB}, {"W_SOLCOEFF", W_SOLCOEFF}, {"TB_ST_MAXSTEPS", TB_ST_MAXSTEPS},
+        {"TB_ST_ZERO_STEP", TB_ST_ZERO_STEP}, {"TB_ST_NONFINITE", TB_ST_NONFINITE}};
+    for (auto &kv : ops) { snprintf(buf, sizeof buf, " %s = %d,", kv.first, kv.second); s += buf; }
+    s += " TB_W2_ENUM_END };\n";
+    s += tb::embedded_math_h();
+    s += tb::embedded_wide2_dev();
+    line("%s", "template <bool FAST>");
+    line("%s", "__device__ __forceinline__ void tb_w2_groups(const W2Args &a, double *__restrict__ W, double *__restrict__ tr, const double *par,");
+    line("%s", "                                             const double *__restrict__ lcc, const double *__restrict__ gnum, const int k, const int tid,");
+    line("%s", "                                             const double *lcreg) {");
+    for (size_t g = 0; g < w->g_count.size(); g++) {
+        line("  /* group %zu: %d clusters x %d entries */", g, w->g_count[g], w->g_len[g]);
+        if (w->g_count[g] <= w->threads) line("  if (tid < %d) { const int r = tid;", w->g_count[g]);
+        else line("  for (int r = tid; r < %d; r += TB_W2_THREADS) {", w->g_count[g]);
+        for (int j = 0; j < w->g_len[g]; j++) {
+            const C2Op &o = w->gops[w->g_off[g] + j];
+            long long no;
+            memcpy(&no, &o.immb, sizeof no);
+            const bool lit = (o.a == -1 && o.para < 0) || (o.b == -1 && o.parb < 0);
+            auto fld = [&](int v, int bit) { return std::to_string(v) + ((o.flags & bit) ? " + r" : ""); };
+            std::string e = "    { C2Op o; o.op = " + std::to_string(o.op) + "; o.res = " + fld(o.res, 16) + "; o.a = " + fld(o.a, 32) +
+                            "; o.b = " + fld(o.b, 64) + "; o.aux = " + fld(o.aux, 128) + "; o.flags = " + std::to_string(o.flags & 15) +
+                            "; o.para = " + std::to_string(o.para) + "; o.parb = " + std::to_string(o.parb) + ";";
+            s += e + "\n";
+            snprintf(buf, sizeof buf, "      o.lc_off = %d + r; o.lc_n = %d; o.lc_stride = %d; o.lc_soff = %s; o.lc_sstride = %d; o.pad = %d; o.imm = %a;",
+                     o.lc_off, o.lc_n, o.lc_stride, fld(o.lc_soff, 256).c_str(), o.lc_sstride, o.pad, o.imm);
+            s += buf; s += '\n';
+            if (lit) line("      o.imma = o.immb = gnum[%lld + r];", no);
+            else line("      o.imma = o.immb = %s;", "0.0");
+            if (const Cached *c = find_cached(g, j)) line("      exec2<FAST>(a, W, tr, par, lcc, %s, o, k, lcreg + %d, %d); }", lc_smem ? "true" : "false", c->off, c->n);
+            else line("      exec2<FAST>(a, W, tr, par, lcc, %s, o, k); }", lc_smem ? "true" : "false");
+        }
+        line("  %s", "}");
+    }
+    line("%s", "}");
+    line("%s", "__device__ __forceinline__ void tb_w2_lcreg_fill(double *lcreg, const double *__restrict__ lcc, const int tid) {");
+    for (auto &c : cached) {
+        const C2Op &o = w->gops[w->g_off[c.g] + c.j];
+        line("  { const int r = tid < %d ? tid : 0; /* group %zu entry %d: %d of %d terms */", w->g_count[c.g], c.g, c.j, c.n, o.lc_n);
+        line("    _Pragma(\"unroll\") for (int u = 0; u < %d; u++) lcreg[%d + u] = lcc[%d + r + u * %d]; }", c.n, c.off, o.lc_off, o.lc_stride);
+    }
+    line("%s", "}");
+    line("extern \"C\" __global__ void __launch_bounds__(%d, %d) tb_w2_kernel(const W2Args a) { wide2_body<%s>(a); }", w->threads, ctas,
+         w->mode == TB_MODE_FAST ? "true" : "false");
+    return s;
 }
 
 void wide2_free(Wide2 *w) {
     if (!w) return;
+    for (auto &kv : w->gen_loaded) tb::module_unload(kv.second.first);
     if (w->d_ops) { cudaFree(w->d_ops); cudaFree(w->d_lcc); cudaFree(w->d_lcs); cudaFree(w->d_xs); cudaFree(w->d_len); cudaFree(w->d_gops); cudaFree(w->d_gnum); }
     delete w;
 }
@@ -820,10 +544,21 @@ void wide2_info(const Wide2 *w, int *nclusters, int *npersist, int *ntransient, 
     if (npersist) *npersist = w->NS;
     if (ntransient) *ntransient = w->ntr;
     if (threads) *threads = w->threads;
-    if (smem_bytes) *smem_bytes = (int)w->smem;
-    if (ctas_per_sm) *ctas_per_sm = w->ctas;
+    const bool gen = !w->gen_cubin.empty();
+    if (smem_bytes) *smem_bytes = (int)(gen ? w->gen_smem : w->smem);
+    if (ctas_per_sm) *ctas_per_sm = gen ? w->gen_ctas : w->ctas;
     if (ngroups) *ngroups = w->gops.empty() ? 0 : (int)w->g_count.size();
 }
+
+void wide2_gen_info(const Wide2 *w, int *generated, int *regs, int *local_bytes, int *lc_in_smem) {
+    const bool gen = w && !w->gen_cubin.empty();
+    if (generated) *generated = gen ? 1 : 0;
+    if (regs) *regs = gen ? w->gen_regs : 0;
+    if (local_bytes) *local_bytes = gen ? w->gen_local : 0;
+    if (lc_in_smem) *lc_in_smem = gen ? (w->gen_lc_smem ? 1 : 0) : (w && w->lc_smem ? 1 : 0);
+}
+const char *wide2_gen_source(const Wide2 *w) { return w ? w->gen_source.c_str() : nullptr; }
+const char *wide2_gen_log(const Wide2 *w) { return w ? w->gen_log.c_str() : nullptr; }
 
 int wide2_integrate(Wide2 *w, long long N, const double *q0, const double *params, double t0, double tmax,
                     const double *trange, long long nt, const tb_opts_t *o, const tb_out_t *out) {
@@ -850,8 +585,21 @@ int wide2_integrate(Wide2 *w, long long N, const double *q0, const double *param
         if (fast) TB_CUDA2(cudaFuncSetAttribute(wide2_kernel<true>, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)w->smem));
         else TB_CUDA2(cudaFuncSetAttribute(wide2_kernel<false>, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)w->smem));
     }
+    const bool gen = !w->gen_cubin.empty();
+    void *gen_fn = nullptr;
+    if (gen) { /* the specialised kernel: one module per device */
+        auto it = w->gen_loaded.find(dev);
+        if (it == w->gen_loaded.end()) {
+            void *mod = nullptr, *fn = nullptr;
+            const int lrc = tb::module_load(w->gen_cubin, "tb_w2_kernel", w->gen_smem, &mod, &fn);
+            if (lrc != TB_OK) return lrc;
+            it = w->gen_loaded.emplace(dev, std::make_pair(mod, fn)).first;
+        }
+        gen_fn = it->second.second;
+    }
     int bps = 1;
-    if (fast) TB_CUDA2(cudaOccupancyMaxActiveBlocksPerMultiprocessor(&bps, wide2_kernel<true>, w->threads, w->smem));
+    if (gen) bps = w->gen_ctas;
+    else if (fast) TB_CUDA2(cudaOccupancyMaxActiveBlocksPerMultiprocessor(&bps, wide2_kernel<true>, w->threads, w->smem));
     else TB_CUDA2(cudaOccupancyMaxActiveBlocksPerMultiprocessor(&bps, wide2_kernel<false>, w->threads, w->smem));
     bps = std::max(1, bps);
     const long long blocks = std::min<long long>((long long)nsm * bps, N);
@@ -860,6 +608,7 @@ int wide2_integrate(Wide2 *w, long long N, const double *q0, const double *param
     a.ops = w->d_ops; a.lc_coef = w->d_lcc; a.lc_ser = w->d_lcs; a.xsid = w->d_xs; a.cl_len = w->d_len; a.lc_smem = w->lc_smem ? 1 : 0; a.lc_count = (int)w->lc_coef.size();
     a.ngroups = w->gops.empty() ? 0 : (int)w->g_count.size(); a.gops = w->d_gops; a.gnum = w->d_gnum;
     a.g_smem = w->g_smem ? 1 : 0; a.ngops = (int)w->gops.size(); a.ngnum = (int)w->gnum.size();
+    if (gen) { a.lc_smem = w->gen_lc_smem ? 1 : 0; a.g_smem = w->gnum.empty() ? 0 : 1; a.ngops = 0; }
     for (int g = 0; g < a.ngroups; g++) { a.g_first[g] = w->g_first[g]; a.g_count[g] = w->g_count[g]; a.g_off[g] = w->g_off[g]; a.g_len[g] = w->g_len[g]; }
     a.nt = trange ? nt : 0; a.t0 = t0; a.tmax = tmax; a.abstol = o->abstol; a.reltol = o->reltol; a.minstep = o->minstepsize;
     a.maxstep = o->maxstepsize; a.maxsteps = o->maxsteps; a.params_per_traj = o->params_per_traj;
@@ -892,10 +641,11 @@ int wide2_integrate(Wide2 *w, long long N, const double *q0, const double *param
         cudaEventCreate(&e0);
         cudaEventCreate(&e1);
         cudaEventRecord(e0, 0);
-        if (fast) wide2_kernel<true><<<(unsigned)blocks, w->threads, w->smem>>>(a);
+        if (gen) { const int lrc = tb::launch_fn(gen_fn, (unsigned)blocks, (unsigned)w->threads, w->gen_smem, nullptr, &a); if (lrc != TB_OK) rc = lrc; }
+        else if (fast) wide2_kernel<true><<<(unsigned)blocks, w->threads, w->smem>>>(a);
         else wide2_kernel<false><<<(unsigned)blocks, w->threads, w->smem>>>(a);
         cudaEventRecord(e1, 0);
-        tb::count_launch(1);
+        if (!gen) tb::count_launch(1);
         fail(cudaGetLastError(), "wide2_kernel launch");
         fail(cudaDeviceSynchronize(), "wide2_kernel");
         float ms = -1.f;

@@ -30,6 +30,9 @@ struct Wide2; /* tb_wide2.cu */
 Wide2 *wide2_build(const Program &p, std::string &why);   /* nullptr: the cluster kernel does not apply (why says so) */
 void wide2_free(Wide2 *w);
 void wide2_info(const Wide2 *w, int *nclusters, int *npersist, int *ntransient, int *threads, int *smem_bytes, int *ctas_per_sm, int *ngroups);
+void wide2_gen_info(const Wide2 *w, int *generated, int *regs, int *local_bytes, int *lc_in_smem);
+const char *wide2_gen_source(const Wide2 *w);
+const char *wide2_gen_log(const Wide2 *w);
 int wide2_integrate(Wide2 *w, long long N, const double *q0, const double *params, double t0, double tmax,
                     const double *trange, long long nt, const tb_opts_t *o, const tb_out_t *out);
 

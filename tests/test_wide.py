@@ -90,6 +90,11 @@ def test_cluster_layout_of_the_shared_memory_kernel():
     info = api.WideKernel(P.manyspin_tape(100), 25).info()
     assert info["threads"] == 128 and info["stored_series"] == 400 and info["scalar_slots"] <= 4
     assert info["smem_bytes"] <= 110 * 1024 and info["ctas_per_sm"] == 2 and info["groups"] == 2
+    # the two group programs are specialised by NVRTC (straight-line entries, the head of the coupling constants in
+    # registers, the rest through L1/L2): no spills
+    wk = api.WideKernel(P.manyspin_tape(100), 25)
+    assert info["generated"] == 1 and info["local_bytes"] == 0 and info["coupling_in_smem"] == 0
+    assert "tb_w2_groups" in wk.source and "tb_w2_kernel" in wk.log
     k = api.WideKernel(P.kepler_tape(), 28).info()   # one cluster: everything depends on r^3
     assert k["threads"] == 32 and k["stored_series"] >= 8
 
