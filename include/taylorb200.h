@@ -361,6 +361,21 @@ int tb_tn_monomials(const tb_tn_t *t, int32_t *expo);
 int tb_tn_integrate(tb_tn_t *t, int64_t N, const double *q0, const double *params, double t0, double tmax,
                     const double *trange, int64_t nt, const tb_opts_t *opts, const tb_tn_out_t *out);
 
+/* The same TaylorN integration for callers that cannot allocate (code under CUDA graph capture, tight serving loops,
+ * harnesses that forbid cudaMalloc).  No counterpart in the reference.
+ * q0 / params / trange and every pointer of `d_out` are DEVICE buffers of the caller (layouts as above; xv_trange is
+ * used only with a trange); everything else the kernel needs -- work-queue counter, device copies of the tape and the
+ * index tables, the jet workspace -- lives in one static device array of TB_TN_STATIC_SCRATCH_BYTES inside the library
+ * (every GPU that loads the library holds it until exit).  The call allocates and frees nothing, enqueues clears,
+ * table copies and ONE kernel on `stream` (a cudaStream_t, NULL = default stream) and returns without synchronising.
+ * The grid shrinks to the CTAs whose workspace fits (same results: trajectories come from a shared queue); a problem
+ * whose single trajectory does not fit returns TB_ERR_UNSUPPORTED with the sizes in tb_last_error.
+ * All calls share the array: calls that overlap on the GPU (two streams, two host threads) race -- serialise them. */
+#define TB_TN_STATIC_SCRATCH_BYTES (16u << 20)
+int tb_tn_integrate_static(tb_tn_t *t, int64_t N, const double *d_q0, const double *d_params, double t0, double tmax,
+                           const double *d_trange, int64_t nt, const tb_opts_t *opts, const tb_tn_out_t *d_out,
+                           void *stream);
+
 /* ---- large-state ODEs (one CTA per trajectory) -----------------------------------
  * Same drivers (taylorinteg.jl:329-381, 582-642) for tapes too large for one thread:
  * hundreds of components, 10^4 entries (spin_odes!, benchmark/manyspin_benchmarks.jl:10-41).

@@ -16,6 +16,8 @@
 #include <cuda_runtime.h>
 
 #include <cstdint>
+#include <map>
+#include <mutex>
 #include <string>
 #include <vector>
 
@@ -632,3 +634,113 @@ int tb_tn_integrate(tb_tn_t *t, int64_t N, const double *q0, const double *param
 }
 
 } /* extern "C" */
+
+/* ---- no-allocation entry point ------------------------------------------------------------------------------
+ * tb_tn_integrate_static: the same tn_kernel, for callers that cannot call cudaMalloc (code under CUDA graph capture,
+ * tight serving loops, harnesses that forbid it).  Everything tb_tn_integrate allocates per call -- the work-queue
+ * counter, the device copies of the tape and the index tables, and the jet workspace [blocks][nser][P+1][nc] -- lives in
+ * ONE file-scope device array of TB_TN_STATIC_SCRATCH_BYTES; inputs and outputs are the caller's DEVICE buffers.
+ * In host code `tn_static_scratch` is only a stand-in for the symbol: its device address is resolved once per device
+ * with cudaGetSymbolAddress (that device current) and that pointer is what the kernel receives.
+ * Every call shares the array and finds the previous call's contents in it: the counter and the part of the workspace
+ * this call uses are cleared on the caller's stream before the launch, the tables are re-sent every call.  Two calls
+ * that overlap on the GPU (different streams, different host threads) race on it: serialise them.                 */
+static __device__ __align__(256) unsigned char tn_static_scratch[TB_TN_STATIC_SCRATCH_BYTES];
+
+namespace {
+std::mutex tn_static_mu;
+std::map<int, unsigned char *> tn_static_addr; /* device -> device address of tn_static_scratch */
+
+int tn_static_base(int dev, unsigned char **base) {
+    std::lock_guard<std::mutex> lk(tn_static_mu);
+    auto it = tn_static_addr.find(dev);
+    if (it == tn_static_addr.end()) {
+        unsigned char *ptr = nullptr;
+        const cudaError_t e = cudaGetSymbolAddress((void **)&ptr, tn_static_scratch); /* device `dev` is current */
+        if (e != cudaSuccess || !ptr) {
+            tb::set_error(std::string("tb_tn_integrate_static: cudaGetSymbolAddress(tn_static_scratch): ") + cudaGetErrorString(e));
+            return TB_ERR_CUDA;
+        }
+        it = tn_static_addr.emplace(dev, ptr).first;
+    }
+    *base = it->second;
+    return TB_OK;
+}
+} // namespace
+
+extern "C" int tb_tn_integrate_static(tb_tn_t *t, int64_t N, const double *d_q0, const double *d_params, double t0, double tmax,
+                                      const double *d_trange, int64_t nt, const tb_opts_t *o, const tb_tn_out_t *d_out,
+                                      void *stream) {
+    if (!t || !d_q0 || !o || !d_out || N < 0 || (d_trange && nt < 2)) { tb::set_error("tb_tn_integrate_static: bad argument"); return TB_ERR_ARG; }
+    const tb_ode_desc_t &d = t->ode.desc;
+    if (d.npar > 0 && !d_params) { tb::set_error("tb_tn_integrate_static: the ODE has parameters, d_params is NULL"); return TB_ERR_ARG; }
+    if (N == 0) return TB_OK;
+    cudaStream_t st = (cudaStream_t)stream;
+    int dev = 0, nsm = 148, bps = 1;
+    TB_CUDA(cudaGetDevice(&dev));
+    const int nc = t->T.ncoef, P = t->order;
+    const size_t np = t->T.pair_a.size();
+    const int threads = ((nc + 31) / 32) * 32;
+    size_t smem = sizeof(double) * nc * 7;
+    const bool pairs_in_smem = smem + 4 * np <= 100 * 1024;
+    if (pairs_in_smem) smem += 4 * np;
+    const bool fast = t->mode == TB_MODE_FAST;
+    if (fast) TB_CUDA(cudaFuncSetAttribute(tn_kernel<true>, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)smem));
+    else TB_CUDA(cudaFuncSetAttribute(tn_kernel<false>, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)smem));
+    if (fast) TB_CUDA(cudaOccupancyMaxActiveBlocksPerMultiprocessor(&bps, tn_kernel<true>, threads, smem));
+    else TB_CUDA(cudaOccupancyMaxActiveBlocksPerMultiprocessor(&bps, tn_kernel<false>, threads, smem));
+    TB_CUDA(cudaDeviceGetAttribute(&nsm, cudaDevAttrMultiProcessorCount, dev));
+    bps = bps < 1 ? 1 : (bps > 16 ? 16 : bps);
+    /* layout of the array: counter | tape | degrees | pair offsets | packed pairs | pair_a | pair_b | workspace */
+    auto up = [](size_t v) { return (v + 255) & ~(size_t)255; };
+    const int nser = 2 * d.dof + d.ntmp + 1;
+    const size_t o_ctr = 0, o_ops = 256, o_deg = o_ops + up(sizeof(tb_op_t) * (size_t)d.nops), o_off = o_deg + up((size_t)nc),
+                 o_pab = o_off + up(sizeof(int) * (size_t)(nc + 1)), o_pa = o_pab + up(4 * np), o_pb = o_pa + up(2 * np),
+                 o_work = o_pb + up(2 * np);
+    const size_t per_block = sizeof(double) * (size_t)nser * (size_t)(P + 1) * (size_t)nc;
+    if (o_work + per_block > (size_t)TB_TN_STATIC_SCRATCH_BYTES) {
+        tb::set_error("tb_tn_integrate_static: one trajectory needs " + std::to_string(o_work + per_block) +
+                      " bytes of scratch (tables + " + std::to_string(nser) + " jets x " + std::to_string(P + 1) + " x " +
+                      std::to_string(nc) + " coefficients), more than TB_TN_STATIC_SCRATCH_BYTES = " +
+                      std::to_string((size_t)TB_TN_STATIC_SCRATCH_BYTES) + "; use tb_tn_integrate");
+        return TB_ERR_UNSUPPORTED;
+    }
+    long long blocks = (long long)nsm * bps;
+    if (blocks > N) blocks = N;
+    const long long fit = (long long)(((size_t)TB_TN_STATIC_SCRATCH_BYTES - o_work) / per_block);
+    if (blocks > fit) blocks = fit; /* fewer resident CTAs than tb_tn_integrate would use: same results, the queue is shared */
+    unsigned char *base = nullptr;
+    const int src = tn_static_base(dev, &base);
+    if (src != TB_OK) return src;
+    /* packed pairs (host-side scratch of this thread; the copies below are staged before cudaMemcpyAsync returns) */
+    static thread_local std::vector<unsigned int> pab;
+    pab.resize(np);
+    for (size_t q = 0; q < np; q++) pab[q] = (unsigned int)t->T.pair_a[q] | ((unsigned int)t->T.pair_b[q] << 16);
+    TB_CUDA(cudaMemsetAsync(base + o_ctr, 0, 256, st));
+    TB_CUDA(cudaMemsetAsync(base + o_work, 0, per_block * (size_t)blocks, st));
+    if (d.nops > 0) TB_CUDA(cudaMemcpyAsync(base + o_ops, t->ode.ops.data(), sizeof(tb_op_t) * (size_t)d.nops, cudaMemcpyHostToDevice, st));
+    TB_CUDA(cudaMemcpyAsync(base + o_deg, t->T.deg.data(), (size_t)nc, cudaMemcpyHostToDevice, st));
+    TB_CUDA(cudaMemcpyAsync(base + o_off, t->T.pair_off.data(), sizeof(int) * (size_t)(nc + 1), cudaMemcpyHostToDevice, st));
+    if (np > 0) {
+        TB_CUDA(cudaMemcpyAsync(base + o_pab, pab.data(), 4 * np, cudaMemcpyHostToDevice, st));
+        TB_CUDA(cudaMemcpyAsync(base + o_pa, t->T.pair_a.data(), 2 * np, cudaMemcpyHostToDevice, st));
+        TB_CUDA(cudaMemcpyAsync(base + o_pb, t->T.pair_b.data(), 2 * np, cudaMemcpyHostToDevice, st));
+    }
+    TnArgs a{};
+    a.N = N; a.dof = d.dof; a.npar = d.npar; a.ntmp = d.ntmp; a.nops = d.nops; a.P = P; a.nc = nc; a.d = t->varorder; a.nser = nser;
+    a.ops = (const tb_op_t *)(base + o_ops); a.deg = base + o_deg; a.pair_off = (const int *)(base + o_off);
+    a.pair_a = (const unsigned short *)(base + o_pa); a.pair_b = (const unsigned short *)(base + o_pb);
+    a.pair_ab = (const unsigned int *)(base + o_pab); a.npairs = (int)np; a.pairs_in_smem = pairs_in_smem ? 1 : 0;
+    a.q0 = d_q0; a.params = d_params; a.trange = d_trange; a.nt = d_trange ? nt : 0; a.t0 = t0; a.tmax = tmax;
+    a.abstol = o->abstol; a.reltol = o->reltol; a.minstep = o->minstepsize; a.maxstep = o->maxstepsize; a.maxsteps = o->maxsteps;
+    a.params_per_traj = o->params_per_traj;
+    a.work = (double *)(base + o_work);
+    a.xfinal = d_out->xfinal; a.tfinal = d_out->tfinal; a.nsteps = (long long *)d_out->nsteps; a.status = d_out->status;
+    a.xv_trange = d_trange ? d_out->xv_trange : nullptr;
+    a.counter = (unsigned long long *)(base + o_ctr);
+    if (fast) tn_kernel<true><<<(unsigned)blocks, threads, smem, st>>>(a);
+    else tn_kernel<false><<<(unsigned)blocks, threads, smem, st>>>(a);
+    tb::count_launch(1);
+    TB_CUDA(cudaGetLastError());
+    return TB_OK; /* asynchronous on `stream`: the caller synchronises before reading the outputs */
+}
