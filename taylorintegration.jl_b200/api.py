@@ -477,20 +477,23 @@ def taylorinteg_events(tape: Tape, q0, t0, tmax, order, abstol, params=None, tra
 def lyap_taylorinteg(f, q0, *args, maxsteps: int = 500, parse_eqs: bool = True, reltol: float = 0.0,
                      minstepsize: float = 0.0, maxstepsize: float = np.inf, mode="parity", output=None, kernel_opts=None,
                      devices=None, block: int = 4096):
-    """Lyapunov spectrum (src/lyapunovspectrum.jl:293-429).  The Jacobian always comes from first-order forward
-    mode on the tape (the reference's TaylorN path); `jacobianfunc` is accepted and ignored, since the reference
-    requires both to agree (test/lyapunov.jl:294-296)."""
+    """Lyapunov spectrum (src/lyapunovspectrum.jl:293-429).  Without `jacobianfunc` the Jacobian comes from first-order
+    forward mode on the tape (the reference's TaylorN path, lyapunovspectrum.jl:45-63); a `jacobianfunc(jac, x, p, t)`
+    given after `params` is traced into the tape instead (lyapunovspectrum.jl:65-78).  The reference's own test
+    requires the two to give identical `t`, `x`, `λ` (test/lyapunov.jl:292-296); tests/test_lyap_userjac.py holds that."""
     # (q0, t0, tmax, order, abstol[, params[, jacobianfunc]])  or  (q0, trange, order, abstol[, params[, jacobianfunc]])
     trange = None
     if len(args) >= 1 and np.ndim(args[0]) >= 1:  # src/lyapunovspectrum.jl:431-596
         trange, order, abstol = args[:3]
         params = args[3] if len(args) > 3 else None
+        jacobianfunc = args[4] if len(args) > 4 else None
         t0 = tmax = None
     else:
         t0, tmax, order, abstol = args[:4]
         params = args[4] if len(args) > 4 else None
+        jacobianfunc = args[5] if len(args) > 5 else None
     dof = np.asarray(q0).shape[0]
-    tape = _as_tape(f, dof, params, jacobian=True)
+    tape = _as_tape(f, dof, params, jacobian=jacobianfunc if callable(jacobianfunc) else True)
     if tape.jac is None:
         raise ValueError("the tape has no Jacobian; build it with taylorize(..., jacobian=True)")
     return _integrate(tape, L.KIND_LYAP, q0, t0, tmax, trange, int(order), abstol, params, maxsteps=maxsteps, dense=False,

@@ -504,11 +504,46 @@ class Tape:
         return "\n".join(out)
 
 
-def taylorize(f: Callable, dof: int, npar: int = 0, *, event: Optional[Callable] = None, jacobian: bool = False,
+class _JacMatrix:
+    """`jac` of a user `jacobianfunc!(jac, x, p, t)` (src/lyapunovspectrum.jl:65-78): `jac[i, j] = value` records the
+    entry; a number stays a number (the reference's `-σ + zero(x[1])` constant series multiplies with the same bits)."""
+
+    def __init__(self, tr: _Tracer, dof: int):
+        self.tr, self.dof = tr, dof
+        self.ent = {}
+
+    def __setitem__(self, ij, v) -> None:
+        i, j = ij
+        if not (0 <= i < self.dof and 0 <= j < self.dof):
+            raise IndexError(ij)
+        if isinstance(v, _ParamVector):
+            v = v._scalar()
+        if isinstance(v, (int, float)):
+            self.ent[(i, j)] = (L.JAC_ZERO, 0, 0.0) if v == 0 else (L.JAC_CONST, 0, float(v))
+        elif isinstance(v, Val):
+            if v.kind == L.K_IMM:
+                self.ent[(i, j)] = (L.JAC_ZERO, 0, 0.0) if v.value == 0 else (L.JAC_CONST, 0, float(v.value))
+            elif v.kind == L.K_PAR:
+                self.ent[(i, j)] = (L.JAC_PAR, v.operand, 1.0)
+            else:
+                self.ent[(i, j)] = (L.JAC_SERIES, v.operand, 0.0)
+        else:
+            raise TypeError("a Jacobian entry is a number, a parameter or a series")
+
+    def entries(self):
+        missing = [(i, j) for i in range(self.dof) for j in range(self.dof) if (i, j) not in self.ent]
+        if missing:
+            raise ValueError(f"the Jacobian function does not assign jac{missing}")
+        return [self.ent[(i, j)] for i in range(self.dof) for j in range(self.dof)]
+
+
+def taylorize(f: Callable, dof: int, npar: int = 0, *, event: Optional[Callable] = None, jacobian=False,
               name: Optional[str] = None) -> Tape:
     """Trace `f(dx, x, p, t)` (and optionally an event function `g(dx, x, p, t) -> (gate, series)`) into a Tape.
 
-    `jacobian=True` adds the variational-equation Jacobian needed by `lyap_taylorinteg`.
+    `jacobian=True` adds the variational-equation Jacobian needed by `lyap_taylorinteg` (first-order forward mode on
+    the tape: the reference's TaylorN path, src/lyapunovspectrum.jl:45-63); `jacobian=jf` traces the user's
+    `jf(jac, x, p, t)` instead (the `jacobianfunc!` path, src/lyapunovspectrum.jl:65-78).
     """
     tr = _Tracer(dof, npar)
     x = [Val(tr, L.K_X, i) for i in range(dof)]
@@ -534,7 +569,13 @@ def taylorize(f: Callable, dof: int, npar: int = 0, *, event: Optional[Callable]
             tape.ev_gate_cmp = L.GATE_ALWAYS
         else:
             raise TypeError("the event gate must be `True` or a comparison of a series with 0")
-    if jacobian:
+    if callable(jacobian):
+        tr.cur = 2
+        Jm = _JacMatrix(tr, dof)
+        jacobian(Jm, x, p, t)
+        tape.jac = Jm.entries()
+        tape.jac_ops = tr.segments[2]
+    elif jacobian:
         tr.cur = 2
         J = _Jac(tr)
         J.run(tr.segments[0], dof)
