@@ -373,7 +373,7 @@ def run_b200(a):
     import taylorintegration_b200 as tb
     from taylorintegration_b200 import _lib as L
     from taylorintegration_b200.api import _column_tape
-    from taylorintegration_b200.sharding import shard_indices
+    from taylorintegration_b200.sharding import auto_block, shard_indices
     rank, world = int(os.environ.get("RANK", "0")), int(os.environ.get("WORLD_SIZE", "1"))
     local = int(os.environ.get("LOCAL_RANK", "0"))
     if not torch.cuda.is_available():
@@ -387,7 +387,7 @@ def run_b200(a):
     w = make_workload(a)          # the whole ensemble of this rank (weak) or of the job (strong)
     strong = a.scaling == "strong" and world > 1
     Nglob = w.N
-    own = shard_indices(Nglob, world, rank) if strong else np.arange(Nglob)
+    own = shard_indices(Nglob, world, rank, auto_block(Nglob, world)) if strong else np.arange(Nglob)
     N = int(own.size)
     mode = L.MODE_PARITY if a.mode == "parity" else L.MODE_FAST
     dof = w.dof

@@ -294,7 +294,7 @@ int tb_integrate_trange(tb_kernel_t *k, int64_t N, const double *q0, const doubl
                         const double *trange, int64_t nt, const tb_opts_t *opts, tb_out_t *out);
 
 /* ONE ensemble over several GPUs of this process.  The N trajectories are cut into round-robin blocks
- * of `block` (0 = 4096); device `devices[d]` takes blocks d, d + ndev, ...; one host thread per device runs the
+ * of `block` (0 = 4096, or less for small ensembles so that every device gets about 8 blocks); device `devices[d]` takes blocks d, d + ndev, ...; one host thread per device runs the
  * host-buffer path above on its shard and writes its results straight into the caller's [rows x N] buffers.
  * trange == NULL: the (t0, tmax) drivers; otherwise tb_integrate_trange semantics (t0 / tmax ignored).  All outputs of
  * tb_out_t are supported.  tb_last_kernel_ms() afterwards reports the slowest device's kernel.  The reference has no

@@ -799,7 +799,7 @@ int tb_integrate_multi(tb_kernel_t *k, const int32_t *devices, int32_t ndev, int
                        const double *params, double t0, double tmax, const double *trange, int64_t nt,
                        const tb_opts_t *opts, tb_out_t *out) {
     if (!devices || ndev < 1) { set_error("tb_integrate_multi: no devices"); return TB_ERR_ARG; }
-    if (block <= 0) block = 4096;
+    if (block <= 0) block = std::max<int64_t>(1, std::min<int64_t>(4096, (N + 8 * (int64_t)ndev - 1) / (8 * (int64_t)ndev))); /* >= ~8 blocks per device */
     int rc = check_call("tb_integrate_multi", k, N, q0, params, trange, nt, opts, out);
     if (rc) return rc;
     if (trange) { t0 = trange[0]; tmax = trange[nt - 1]; }

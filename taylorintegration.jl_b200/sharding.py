@@ -20,6 +20,12 @@ import numpy as np
 from .api import EnsembleSolution
 
 
+def auto_block(N: int, world: int, block: int = 4096) -> int:
+    """Block size that gives every rank at least ~8 blocks: `block` for large ensembles, smaller for small ones (a 2^14
+    TaylorN ensemble over 8 ranks with blocks of 4096 would leave four ranks empty)."""
+    return int(max(1, min(block, -(-N // (8 * world)))))
+
+
 def shard_indices(N: int, world: int, rank: int, block: int = 4096) -> np.ndarray:
     """Global trajectory indices owned by `rank`: blocks rank, rank+world, rank+2*world, ... of `block` trajectories."""
     if not (0 <= rank < world):
@@ -108,6 +114,7 @@ def run_sharded(integrate_local: Callable[[np.ndarray, Optional[np.ndarray]], En
     world, rank = dist.get_world_size(group), dist.get_rank(group)
     q0 = np.asarray(q0, dtype=np.float64)
     N = q0.shape[1]
+    block = auto_block(N, world, block)  # small ensembles: smaller blocks, so that no rank stays empty
     idx = shard_indices(N, world, rank, block)
     p = None if params is None else np.asarray(params, dtype=np.float64)
     p_loc = p if p is None or p.ndim == 1 else np.ascontiguousarray(p[:, idx])

@@ -129,3 +129,11 @@ def test_two_rank_sharded_taylorinteg_on_gpu(tmp_path):
     for r in range(2):
         z = np.load(tmp_path / f"g{r}.npz")
         assert np.array_equal(z["x"], ref.xfinal) and np.array_equal(z["n"], ref.nsteps) and not z["s"].any()
+
+
+def test_auto_block_leaves_no_rank_empty():
+    # 2^14 TaylorN neighbourhoods over 8 ranks: blocks of 4096 would feed four ranks only
+    assert S.auto_block(1 << 20, 8) == 4096 and S.auto_block(1 << 14, 8) == 256 and S.auto_block(5, 8) == 1
+    for N, world in ((1 << 14, 8), (2048, 8), (100, 3), (8, 8)):
+        sizes = S.shard_sizes(N, world, S.auto_block(N, world))
+        assert sizes.sum() == N and sizes.min() >= 1 and sizes.max() - sizes.min() <= S.auto_block(N, world)
