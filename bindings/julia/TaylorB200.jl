@@ -49,7 +49,8 @@ mutable struct TbOut
     xv_trange::Ptr{Float64}; tv::Ptr{Float64}; xv::Ptr{Float64}; psol::Ptr{Float64}
     tevents::Ptr{Float64}; xevents::Ptr{Float64}; gresids::Ptr{Float64}; nevents::Ptr{Int32}
     lambda::Ptr{Float64}; lambda_v::Ptr{Float64}
-    TbOut() = new(ntuple(_ -> C_NULL, 14)...)
+    lyap_state::Ptr{Float64}; lyap_state0::Ptr{Float64}   # Lyapunov continue-from-state (out / in)
+    TbOut() = new(ntuple(_ -> C_NULL, 16)...)
 end
 
 const OP = (IDENTITY = 1, NEG = 2, ADD = 3, SUB = 4, MUL = 5, DIV = 6, SQR = 7, SQRT = 8, POW = 9, EXP = 10,

@@ -49,7 +49,7 @@
 extern "C" {
 #endif
 
-#define TB_ABI_VERSION 1
+#define TB_ABI_VERSION 2
 
 /* ---- return codes -------------------------------------------------------- */
 enum tb_status {
@@ -250,6 +250,14 @@ typedef struct tb_out {
     /* Lyapunov: lyapunovspectrum.jl:411-415                                  */
     double *lambda;    /* [dof x N]   exponents at tfinal                     */
     double *lambda_v;  /* [dof x stride x N] per step (with tv/xv), optional  */
+    /* Lyapunov "continue from state" (the state of a run is (t0, x0, λtsum, Q); the reference keeps it
+     * in the cache of lyap_taylorinteg!, lyapunovspectrum.jl:340-429, and has no resume call).  (t0, tmax) drivers only.
+     * Rows [(dof*dof + dof + 1) x N], element (row, i) at row*N + i: rows c*dof + r = Q[r, c] (the orthonormal frame the
+     * variational state was reset to after the last step), rows dof*dof + c = λtsum[c], last row = t00 (start of the
+     * time span the exponents are averaged over).  A second call with q0 = xfinal, t0 = tfinal, lyap_state0 = the
+     * lyap_state of the first continues the run: same arithmetic as one run that had been asked to stop at tfinal. */
+    double *lyap_state;        /* out, optional */
+    const double *lyap_state0; /* in, optional: NULL = fresh run (Q = I, λtsum = 0, t00 = t0) */
 } tb_out_t;
 
 typedef struct tb_ode tb_ode_t;       /* validated tape                       */

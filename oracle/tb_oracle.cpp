@@ -669,7 +669,9 @@ void modifiedGS(const double *A, double *Q, double *R, int n) {
 int integ_lyap(Work &w, const double *q0, double t0, double tmax, const tb_opts_t &o, const StepOut *so,
                double *lambda_v /*[dof x stride] or null*/, double *xfinal, double *tfinal, double *lambda,
                int64_t *nsteps_out, int32_t *status, const double *trange = nullptr, int64_t nt = 0,
-               double *xvtr = nullptr /*[dof x nt]*/, double *lamtr = nullptr /*[dof x nt]*/) {
+               double *xvtr = nullptr /*[dof x nt]*/, double *lamtr = nullptr /*[dof x nt]*/,
+               const double *state0 = nullptr /* continue from state: Q (column-major), lsum[dof], t00 */,
+               double *state_out = nullptr) {
     const tb_ode_desc_t *d = w.d;
     const int dof = d->dof, P = w.P, nx = dof + dof * dof;
     if (!d->has_jac) return TB_ERR_ARG;
@@ -685,11 +687,15 @@ int integ_lyap(Work &w, const double *q0, double t0, double tmax, const tb_opts_
     std::vector<double> x0(nx, 0.0), jt(dof * dof, 0.0), QH(dof * dof), RH(dof * dof), lsum(dof, 0.0), lam(dof, 0.0);
     for (int i = 0; i < dof; i++) x0[i] = q0[i];
     for (int i = 0; i < dof; i++) jt[i + i * dof] = 1.0;
+    if (state0) {
+        for (int i = 0; i < dof * dof; i++) jt[i] = state0[i];
+        for (int i = 0; i < dof; i++) lsum[i] = state0[dof * dof + i];
+    }
     for (int i = 0; i < dof * dof; i++) x0[dof + i] = jt[i];
     /* jac series storage: [dof x dof][P+1] (row i, col j) */
     std::vector<double> jac((size_t)dof * dof * (P + 1), 0.0), vaux(P + 1);
     update_cache(w, t0, x0.data(), nx);
-    double t00 = t0;
+    double t00 = state0 ? state0[dof * dof + dof] : t0;
     if (so && so->tv) so->tv[0] = t0;
     if (so && so->xv) for (int i = 0; i < dof; i++) so->xv[(size_t)i * so->stride] = q0[i];
     if (lambda_v) for (int i = 0; i < dof; i++) lambda_v[(size_t)i * so->stride] = 0.0;
@@ -787,6 +793,11 @@ int integ_lyap(Work &w, const double *q0, double t0, double tmax, const tb_opts_
         if (!fin) { st |= TB_ST_NONFINITE; break; }
     }
     for (int i = 0; i < dof; i++) { xfinal[i] = x0[i]; lambda[i] = lam[i]; }
+    if (state_out) {
+        for (int i = 0; i < dof * dof; i++) state_out[i] = x0[dof + i];
+        for (int i = 0; i < dof; i++) state_out[dof * dof + i] = lsum[i];
+        state_out[dof * dof + dof] = t00;
+    }
     *tfinal = t0;
     *nsteps_out = nsteps - 1;
     *status = st;
@@ -908,9 +919,15 @@ int tbo_integrate(const tb_ode_desc_t *d, int order, int kind, int math_mode, in
             else if (kind == TB_KIND_EVENTS)
                 rc = integ_events(w, q.data(), t0, tmax, o, want_steps ? &so : nullptr, xf.data(), &tf, &ns, &st,
                                   tev.data(), xev.data(), gre.data(), &nev, cap);
-            else if (kind == TB_KIND_LYAP)
+            else if (kind == TB_KIND_LYAP) {
+                const int rows = dof * dof + dof + 1;
+                std::vector<double> s0, s1(rows);
+                if (out->lyap_state0) { s0.resize(rows); for (int r = 0; r < rows; r++) s0[r] = out->lyap_state0[(size_t)r * N + i]; }
                 rc = integ_lyap(w, q.data(), t0, tmax, o, want_steps ? &so : nullptr,
-                                out->lambda_v ? lvl.data() : nullptr, xf.data(), &tf, lam.data(), &ns, &st);
+                                out->lambda_v ? lvl.data() : nullptr, xf.data(), &tf, lam.data(), &ns, &st, nullptr, 0, nullptr,
+                                nullptr, out->lyap_state0 ? s0.data() : nullptr, s1.data());
+                if (out->lyap_state) for (int r = 0; r < rows; r++) out->lyap_state[(size_t)r * N + i] = s1[r];
+            }
 
             else rc = integ_plain(w, q.data(), t0, tmax, o, want_steps ? &so : nullptr, xf.data(), &tf, &ns, &st);
             if (rc) { rcs[tid] = rc; return; }

@@ -82,7 +82,8 @@ _DP = C.POINTER(C.c_double)
 class TbOut(C.Structure):
     _fields_ = [("xfinal", _DP), ("tfinal", _DP), ("nsteps", C.POINTER(C.c_int64)), ("status", C.POINTER(C.c_int32)),
                 ("xv_trange", _DP), ("tv", _DP), ("xv", _DP), ("psol", _DP), ("tevents", _DP), ("xevents", _DP),
-                ("gresids", _DP), ("nevents", C.POINTER(C.c_int32)), ("lambda_", _DP), ("lambda_v", _DP)]
+                ("gresids", _DP), ("nevents", C.POINTER(C.c_int32)), ("lambda_", _DP), ("lambda_v", _DP),
+                ("lyap_state", _DP), ("lyap_state0", _DP)]
 
 
 EXPORTS = [

@@ -282,6 +282,7 @@ class EnsembleSolution:
     lam: Optional[np.ndarray] = None      # [dof, N]
     lam_steps: Optional[np.ndarray] = None  # [dof, stride, N]
     lam_trange: Optional[np.ndarray] = None  # [dof, nt, N]
+    lyap_state: Optional[np.ndarray] = None  # [dof*dof + dof + 1, N]: Q (column-major), running sums, t00 (resume)
 
     def trajectory(self, i: int) -> TaylorSolution:
         ns = int(self.nsteps[i])
@@ -321,7 +322,7 @@ def _warn_status(status: np.ndarray) -> None:
 
 def _integrate(tape: Tape, kind: int, q0, t0, tmax, trange, order, abstol, params, *, maxsteps, dense, reltol,
                minstepsize, maxstepsize, eventorder=0, newtoniter=10, nrabstol=_EPS, event_capacity=0, mode="parity",
-               output=None, kernel_opts=None, devices=None, block=4096):
+               output=None, kernel_opts=None, devices=None, block=4096, lyap_state0=None):
     q0 = np.asarray(q0, dtype=np.float64)
     single = q0.ndim == 1
     q = np.ascontiguousarray(q0[:, None] if single else q0)
@@ -423,6 +424,12 @@ def _integrate(tape: Tape, kind: int, q0, t0, tmax, trange, order, abstol, param
         if kind == L.KIND_LYAP:
             sol.lam = np.empty((dof, N))
             out.lambda_ = sol.lam.ctypes.data_as(L._DP)
+            if devices is None:  # continue-from-state: the Lyapunov state of this call, and the one to resume from
+                sol.lyap_state = np.empty((dof * dof + dof + 1, N))
+                out.lyap_state = sol.lyap_state.ctypes.data_as(L._DP)
+                if lyap_state0 is not None:
+                    ls0 = np.ascontiguousarray(lyap_state0, dtype=np.float64).reshape(dof * dof + dof + 1, N)
+                    out.lyap_state0 = ls0.ctypes.data_as(L._DP)
         if devices is not None:  # one ensemble over several GPUs of this process (tb_integrate_multi)
             dv = np.ascontiguousarray(devices, dtype=np.int32)
             L.check(lib.tb_integrate_multi(k.handle, _ptr(dv), dv.size, int(block), N, _ptr(q), _ptr(par), float(t0),
@@ -476,11 +483,13 @@ def taylorinteg_events(tape: Tape, q0, t0, tmax, order, abstol, params=None, tra
 
 def lyap_taylorinteg(f, q0, *args, maxsteps: int = 500, parse_eqs: bool = True, reltol: float = 0.0,
                      minstepsize: float = 0.0, maxstepsize: float = np.inf, mode="parity", output=None, kernel_opts=None,
-                     devices=None, block: int = 4096):
+                     devices=None, block: int = 4096, resume=None):
     """Lyapunov spectrum (src/lyapunovspectrum.jl:293-429).  Without `jacobianfunc` the Jacobian comes from first-order
     forward mode on the tape (the reference's TaylorN path, lyapunovspectrum.jl:45-63); a `jacobianfunc(jac, x, p, t)`
     given after `params` is traced into the tape instead (lyapunovspectrum.jl:65-78).  The reference's own test
-    requires the two to give identical `t`, `x`, `λ` (test/lyapunov.jl:292-296); tests/test_lyap_userjac.py holds that."""
+    requires the two to give identical `t`, `x`, `λ` (test/lyapunov.jl:292-296); tests/test_lyap_userjac.py holds that.
+    Continue from state: the solution carries `lyap_state` (frame Q, running sums λtsum, start of the
+    averaging span); `lyap_taylorinteg(f, sol.xfinal, sol.tfinal[0], t2, ..., resume=sol.lyap_state)` goes on from there."""
     # (q0, t0, tmax, order, abstol[, params[, jacobianfunc]])  or  (q0, trange, order, abstol[, params[, jacobianfunc]])
     trange = None
     if len(args) >= 1 and np.ndim(args[0]) >= 1:  # src/lyapunovspectrum.jl:431-596
@@ -498,7 +507,7 @@ def lyap_taylorinteg(f, q0, *args, maxsteps: int = 500, parse_eqs: bool = True, 
         raise ValueError("the tape has no Jacobian; build it with taylorize(..., jacobian=True)")
     return _integrate(tape, L.KIND_LYAP, q0, t0, tmax, trange, int(order), abstol, params, maxsteps=maxsteps, dense=False,
                       reltol=reltol, minstepsize=minstepsize, maxstepsize=maxstepsize, mode=mode, output=output,
-                      kernel_opts=kernel_opts, devices=devices, block=block)
+                      kernel_opts=kernel_opts, devices=devices, block=block, lyap_state0=resume)
 
 
 def fp64_peak(seconds: float = 0.5) -> Tuple[float, float]:

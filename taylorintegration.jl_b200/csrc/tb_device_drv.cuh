@@ -423,6 +423,12 @@ __device__ __forceinline__ bool tb_traj_init(TbTraj &T, double *__restrict__ smt
     for (int c = 0; c < TB_DOF * TB_DOF; c++) T.x0[TB_DOF + c] = ((c % TB_DOF) == (c / TB_DOF)) ? 1.0 : 0.0;
 #pragma unroll
     for (int c = 0; c < TB_DOF; c++) { T.lsum[c] = 0.0; T.lam[c] = 0.0; }
+    if (a.lyap_state0) { /* continue from state: frame Q and running sums of the previous call (taylorb200.h) */
+#pragma unroll
+        for (int c = 0; c < TB_DOF * TB_DOF; c++) T.x0[TB_DOF + c] = a.lyap_state0[(long long)c * N + i];
+#pragma unroll
+        for (int c = 0; c < TB_DOF; c++) T.lsum[c] = a.lyap_state0[(long long)(TB_DOF * TB_DOF + c) * N + i];
+    }
 #endif
 #pragma unroll
     for (int j = 0; j < TB_NPAR; j++) T.par[j] = a.params_per_traj ? a.params[(long long)j * N + i] : a.params[j];
@@ -451,7 +457,7 @@ __device__ __forceinline__ bool tb_traj_init(TbTraj &T, double *__restrict__ smt
 #pragma unroll
         for (int c = 0; c < TB_DOF; c++) a.xv[((long long)c * a.stride) * N + i] = T.x0[c];
 #if TB_KIND == 2
-    T.t00 = T.t0;
+    T.t00 = a.lyap_state0 ? a.lyap_state0[(long long)(TB_DOF * TB_DOF + TB_DOF) * N + i] : T.t0;
     if (a.lambda_v)
 #pragma unroll
         for (int c = 0; c < TB_DOF; c++) a.lambda_v[((long long)c * a.stride) * N + i] = 0.0;
@@ -752,6 +758,13 @@ __device__ __forceinline__ void tb_traj_finish(const TbTraj &T, const TbArgs &a)
     if (a.lambda)
 #pragma unroll
         for (int c = 0; c < TB_DOF; c++) a.lambda[(long long)c * N + i] = T.lam[c];
+    if (a.lyap_state) {
+#pragma unroll
+        for (int c = 0; c < TB_DOF * TB_DOF; c++) a.lyap_state[(long long)c * N + i] = T.x0[TB_DOF + c];
+#pragma unroll
+        for (int c = 0; c < TB_DOF; c++) a.lyap_state[(long long)(TB_DOF * TB_DOF + c) * N + i] = T.lsum[c];
+        a.lyap_state[(long long)(TB_DOF * TB_DOF + TB_DOF) * N + i] = T.t00;
+    }
 #endif
 }
 
@@ -861,6 +874,11 @@ __device__ __forceinline__ bool tb_traj_init(TbTraj &T, double *__restrict__ smt
     for (int r = 0; r < TB_NQ; r++) T.x0[TB_NQ + r] = (r == T.lit) ? 1.0 : 0.0;
     T.lsum = 0.0;
     T.lam = 0.0;
+    if (a.lyap_state0) { /* continue from state: this lane's column of Q and its running sum (taylorb200.h) */
+#pragma unroll
+        for (int r = 0; r < TB_NQ; r++) T.x0[TB_NQ + r] = a.lyap_state0[(long long)(T.lit * TB_NQ + r) * N + i];
+        T.lsum = a.lyap_state0[(long long)(TB_NQ * TB_NQ + T.lit) * N + i];
+    }
 #pragma unroll
     for (int j = 0; j < TB_NPAR; j++) T.par[j] = a.params_per_traj ? a.params[(long long)j * N + i] : a.params[j];
     T.nsteps = 1;
@@ -889,7 +907,7 @@ __device__ __forceinline__ bool tb_traj_init(TbTraj &T, double *__restrict__ smt
         T.t1 = 0.0;
     }
     T.sign = copysign(1.0, B_(T.tmax, T.t0));
-    T.t00 = T.t0;
+    T.t00 = a.lyap_state0 ? a.lyap_state0[(long long)(TB_NQ * TB_NQ + TB_NQ) * N + i] : T.t0;
 #if TB_LYAP_TRANGE
     if (a.trange) return !(M_(T.sign, T.t0) < M_(T.sign, T.tmax));
 #endif
@@ -1002,6 +1020,12 @@ __device__ __forceinline__ void tb_traj_finish(const TbTraj &T, const TbArgs &a)
         if (a.status) a.status[i] = T.st;
     }
     if (a.lambda) a.lambda[(long long)T.lit * N + i] = T.lam;
+    if (a.lyap_state) {
+#pragma unroll
+        for (int r = 0; r < TB_NQ; r++) a.lyap_state[(long long)(T.lit * TB_NQ + r) * N + i] = T.x0[TB_NQ + r];
+        a.lyap_state[(long long)(TB_NQ * TB_NQ + T.lit) * N + i] = T.lsum;
+        if (T.lit == 0) a.lyap_state[(long long)(TB_NQ * TB_NQ + TB_NQ) * N + i] = T.t00;
+    }
 }
 
 /* Persistent teams: every team pulls trajectory indices from the global queue (leader lane does the

@@ -117,8 +117,10 @@ struct TbArgs {
     unsigned long long *counter;
     double *xjet;
     double *dtout;
+    double *lyap_state;
+    const double *lyap_state0;
 };
-static_assert(sizeof(TbArgs) == 272, "TbArgs layout must match tb_device_pre.cuh");
+static_assert(sizeof(TbArgs) == 288, "TbArgs layout must match tb_device_pre.cuh");
 
 struct Loaded {
     CUmodule mod = nullptr;
@@ -295,6 +297,8 @@ static void fill_args(TbArgs &a, int64_t N, const double *q0, const double *para
     a.nevents = out.nevents;
     a.lambda = out.lambda;
     a.lambda_v = out.lambda_v;
+    a.lyap_state = out.lyap_state;
+    a.lyap_state0 = out.lyap_state0;
     a.counter = (unsigned long long *)work;
 }
 
@@ -375,6 +379,10 @@ static int check_call(const char *fn, tb_kernel *k, int64_t N, const void *q0, c
         return TB_ERR_ARG;
     }
     if (lyapcol && out->psol) { set_error("TB_KIND_LYAPCOL has no dense output"); return TB_ERR_UNSUPPORTED; }
+    if (out->lyap_state || out->lyap_state0) {
+        if (k->co.kind != TB_KIND_LYAP && !lyapcol) { set_error(f + ": lyap_state / lyap_state0 need a Lyapunov kernel"); return TB_ERR_ARG; }
+        if (trange) { set_error(f + ": continue-from-state is implemented for the (t0, tmax) Lyapunov drivers"); return TB_ERR_UNSUPPORTED; }
+    }
     const int64_t stride = opts->steps_stride ? opts->steps_stride : opts->maxsteps + 1;
     if (!trange && (out->tv || out->xv || out->psol || out->lambda_v) && stride < opts->maxsteps + 1) {
         set_error(f + ": steps_stride must be >= maxsteps + 1");
@@ -446,7 +454,10 @@ static int integrate_host(tb_kernel *k, int64_t N, const double *q0, const doubl
         if (!trange) want(out->lambda_v, (void **)&dv.lambda_v, dof * stride * n * 8, ROWS_STEPS, dof, stride);
         else want(out->lambda_v, (void **)&dv.lambda_v, dof * (size_t)nt * n * 8); /* exponents at trange, [dof x nt x N] */
     }
+    const size_t lyap_rows = dof * dof + dof + 1; /* Q, running sums, t00 */
+    if (k->co.kind == TB_KIND_LYAP || lyapcol) want(out->lyap_state, (void **)&dv.lyap_state, lyap_rows * n * 8);
     size_t total = rup(256) + rup(dof * n * 8) + rup(npar_elems * 8) + rup((size_t)(trange ? nt : 0) * 8);
+    if (out->lyap_state0) total += rup(lyap_rows * n * 8);
     for (auto &it : outs) total += rup(it.bytes);
     /* one host-buffer call at a time per kernel handle: the arena and the work counter belong to the call */
     std::lock_guard<std::mutex> call_lock(device_call_mutex(k));
@@ -461,6 +472,11 @@ static int integrate_host(tb_kernel *k, int64_t N, const double *q0, const doubl
     double *d_par = npar_elems ? A.take<double>(npar_elems) : nullptr;
     double *d_tr = trange ? A.take<double>((size_t)nt) : nullptr;
     for (auto &it : outs) *it.dptr = A.take<char>(it.bytes);
+    if (out->lyap_state0) {
+        double *d_ls0 = A.take<double>(lyap_rows * n);
+        TB_CUDA(cudaMemcpyAsync(d_ls0, out->lyap_state0, lyap_rows * n * 8, cudaMemcpyHostToDevice, st));
+        dv.lyap_state0 = d_ls0;
+    }
     TB_CUDA(cudaMemsetAsync(work, 0, 256, st));
     TB_CUDA(cudaMemcpyAsync(d_q0, q0, dof * n * 8, cudaMemcpyHostToDevice, st));
     if (d_par) TB_CUDA(cudaMemcpyAsync(d_par, params, npar_elems * 8, cudaMemcpyHostToDevice, st));
@@ -799,6 +815,7 @@ int tb_integrate_multi(tb_kernel_t *k, const int32_t *devices, int32_t ndev, int
                        const double *params, double t0, double tmax, const double *trange, int64_t nt,
                        const tb_opts_t *opts, tb_out_t *out) {
     if (!devices || ndev < 1) { set_error("tb_integrate_multi: no devices"); return TB_ERR_ARG; }
+    if (out && (out->lyap_state || out->lyap_state0)) { set_error("tb_integrate_multi: Lyapunov continue-from-state is a one-device call"); return TB_ERR_UNSUPPORTED; }
     if (block <= 0) block = std::max<int64_t>(1, std::min<int64_t>(4096, (N + 8 * (int64_t)ndev - 1) / (8 * (int64_t)ndev))); /* >= ~8 blocks per device */
     int rc = check_call("tb_integrate_multi", k, N, q0, params, trange, nt, opts, out);
     if (rc) return rc;

@@ -84,7 +84,7 @@ def series(tape: tb.Tape, order: int, q0, params, operand: int, with_jac=False, 
 
 
 def integrate(tape: tb.Tape, order: int, q0, t0=0.0, tmax=None, params=None, *, kind=L.KIND_PLAIN, trange=None,
-              steps=False, dense=False, math=MATH_TB, nthreads=1, **kw) -> tb.EnsembleSolution:
+              steps=False, dense=False, math=MATH_TB, nthreads=1, lyap_state0=None, **kw) -> tb.EnsembleSolution:
     """Ensemble run on the CPU oracle with the layout of tb_integrate."""
     d, keep = tape.c_desc()
     q = np.asarray(q0, dtype=np.float64)
@@ -133,6 +133,12 @@ def integrate(tape: tb.Tape, order: int, q0, t0=0.0, tmax=None, params=None, *, 
     if kind == L.KIND_LYAP:
         sol.lam = np.zeros((dof, N))
         out.lambda_ = sol.lam.ctypes.data_as(L._DP)
+        if trange is None:
+            sol.lyap_state = np.zeros((dof * dof + dof + 1, N))
+            out.lyap_state = sol.lyap_state.ctypes.data_as(L._DP)
+            if lyap_state0 is not None:
+                ls0 = np.ascontiguousarray(lyap_state0, dtype=np.float64).reshape(dof * dof + dof + 1, N)
+                out.lyap_state0 = ls0.ctypes.data_as(L._DP)
     rc = lib().tbo_integrate(C.byref(d), order, kind, math, nthreads, N, _p(q), _p(par), float(t0), float(tmax),
                              _p(tr), 0 if tr is None else tr.size, C.byref(o), C.byref(out))
     assert rc == 0, rc

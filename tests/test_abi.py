@@ -20,7 +20,7 @@ def test_every_declared_symbol_is_exported():
     missing = [s for s in sorted(declared) if not hasattr(lib, s)]
     assert not missing, missing
     assert set(L.EXPORTS) <= declared
-    assert lib.tb_abi_version() == 1
+    assert lib.tb_abi_version() == 2  # 2: tb_out_t gained lyap_state / lyap_state0
 
 
 def test_defaults_match_reference_keywords():
