@@ -375,7 +375,7 @@ int tb_tn_integrate(tb_tn_t *t, int64_t N, const double *q0, const double *param
  * used only with a trange); everything else the kernel needs -- work-queue counter, device copies of the tape and the
  * index tables, the jet workspace -- lives in one static device array of TB_TN_STATIC_SCRATCH_BYTES inside the library
  * (every GPU that loads the library holds it until exit).  The call allocates and frees nothing, enqueues clears,
- * table copies and ONE kernel on `stream` (a cudaStream_t, NULL = default stream) and returns without synchronising.
+ * (on the first call of a handle, or after another handle used the array) table copies, and ONE kernel on `stream` (a cudaStream_t, NULL = default stream) and returns without synchronising.
  * The grid shrinks to the CTAs whose workspace fits (same results: trajectories come from a shared queue); a problem
  * whose single trajectory does not fit returns TB_ERR_UNSUPPORTED with the sizes in tb_last_error.
  * All calls share the array: calls that overlap on the GPU (two streams, two host threads) race -- serialise them. */

@@ -15,6 +15,7 @@
  */
 #include <cuda_runtime.h>
 
+#include <atomic>
 #include <cstdint>
 #include <map>
 #include <mutex>
@@ -484,6 +485,7 @@ struct tb_tn {
     int *d_off = nullptr;
     unsigned short *d_pa = nullptr, *d_pb = nullptr;
     unsigned int *d_pab = nullptr;
+    unsigned long long serial = 0; /* identity of this handle (tb_tn_integrate_static: whose tables sit in the static array) */
 };
 
 extern "C" {
@@ -513,6 +515,8 @@ tb_tn_t *tb_tn_create(const tb_ode_t *ode, int order, int nvars, int varorder, i
     t->order = order; t->nvars = nvars; t->varorder = varorder; t->mode = mode;
     t->T = tbtn::make_tables(nvars, varorder);
     if (t->T.ncoef > 1024) { tb::set_error("tb_tn_create: more than 1024 polynomial coefficients"); delete t; return nullptr; }
+    static std::atomic<unsigned long long> next_serial{1};
+    t->serial = next_serial++;
     return t;
 }
 
@@ -643,13 +647,14 @@ int tb_tn_integrate(tb_tn_t *t, int64_t N, const double *q0, const double *param
  * In host code `tn_static_scratch` is only a stand-in for the symbol: its device address is resolved once per device
  * with cudaGetSymbolAddress (that device current) and that pointer is what the kernel receives.
  * Every call shares the array and finds the previous call's contents in it: the counter and the part of the workspace
- * this call uses are cleared on the caller's stream before the launch, the tables are re-sent every call.  Two calls
+ * this call uses are cleared on the caller's stream before the launch, the tables are sent again whenever another handle used the array in between.  Two calls
  * that overlap on the GPU (different streams, different host threads) race on it: serialise them.                 */
 static __device__ __align__(256) unsigned char tn_static_scratch[TB_TN_STATIC_SCRATCH_BYTES];
 
 namespace {
 std::mutex tn_static_mu;
 std::map<int, unsigned char *> tn_static_addr; /* device -> device address of tn_static_scratch */
+std::map<int, unsigned long long> tn_static_owner; /* device -> serial of the handle whose tables are in the array */
 
 int tn_static_base(int dev, unsigned char **base) {
     std::lock_guard<std::mutex> lk(tn_static_mu);
@@ -712,19 +717,29 @@ extern "C" int tb_tn_integrate_static(tb_tn_t *t, int64_t N, const double *d_q0,
     unsigned char *base = nullptr;
     const int src = tn_static_base(dev, &base);
     if (src != TB_OK) return src;
-    /* packed pairs (host-side scratch of this thread; the copies below are staged before cudaMemcpyAsync returns) */
-    static thread_local std::vector<unsigned int> pab;
-    pab.resize(np);
-    for (size_t q = 0; q < np; q++) pab[q] = (unsigned int)t->T.pair_a[q] | ((unsigned int)t->T.pair_b[q] << 16);
     TB_CUDA(cudaMemsetAsync(base + o_ctr, 0, 256, st));
     TB_CUDA(cudaMemsetAsync(base + o_work, 0, per_block * (size_t)blocks, st));
-    if (d.nops > 0) TB_CUDA(cudaMemcpyAsync(base + o_ops, t->ode.ops.data(), sizeof(tb_op_t) * (size_t)d.nops, cudaMemcpyHostToDevice, st));
-    TB_CUDA(cudaMemcpyAsync(base + o_deg, t->T.deg.data(), (size_t)nc, cudaMemcpyHostToDevice, st));
-    TB_CUDA(cudaMemcpyAsync(base + o_off, t->T.pair_off.data(), sizeof(int) * (size_t)(nc + 1), cudaMemcpyHostToDevice, st));
-    if (np > 0) {
-        TB_CUDA(cudaMemcpyAsync(base + o_pab, pab.data(), 4 * np, cudaMemcpyHostToDevice, st));
-        TB_CUDA(cudaMemcpyAsync(base + o_pa, t->T.pair_a.data(), 2 * np, cudaMemcpyHostToDevice, st));
-        TB_CUDA(cudaMemcpyAsync(base + o_pb, t->T.pair_b.data(), 2 * np, cudaMemcpyHostToDevice, st));
+    /* the tape and the index tables are sent when another handle (or nobody) used the array last on this device: the
+     * calls after the first of a handle enqueue two clears and the kernel, nothing else */
+    bool resident;
+    {
+        std::lock_guard<std::mutex> lk(tn_static_mu);
+        resident = tn_static_owner.count(dev) && tn_static_owner[dev] == t->serial;
+        tn_static_owner[dev] = t->serial;
+    }
+    if (!resident) {
+        /* packed pairs (host-side scratch of this thread; pageable copies are staged before cudaMemcpyAsync returns) */
+        static thread_local std::vector<unsigned int> pab;
+        pab.resize(np);
+        for (size_t q = 0; q < np; q++) pab[q] = (unsigned int)t->T.pair_a[q] | ((unsigned int)t->T.pair_b[q] << 16);
+        if (d.nops > 0) TB_CUDA(cudaMemcpyAsync(base + o_ops, t->ode.ops.data(), sizeof(tb_op_t) * (size_t)d.nops, cudaMemcpyHostToDevice, st));
+        TB_CUDA(cudaMemcpyAsync(base + o_deg, t->T.deg.data(), (size_t)nc, cudaMemcpyHostToDevice, st));
+        TB_CUDA(cudaMemcpyAsync(base + o_off, t->T.pair_off.data(), sizeof(int) * (size_t)(nc + 1), cudaMemcpyHostToDevice, st));
+        if (np > 0) {
+            TB_CUDA(cudaMemcpyAsync(base + o_pab, pab.data(), 4 * np, cudaMemcpyHostToDevice, st));
+            TB_CUDA(cudaMemcpyAsync(base + o_pa, t->T.pair_a.data(), 2 * np, cudaMemcpyHostToDevice, st));
+            TB_CUDA(cudaMemcpyAsync(base + o_pb, t->T.pair_b.data(), 2 * np, cudaMemcpyHostToDevice, st));
+        }
     }
     TnArgs a{};
     a.N = N; a.dof = d.dof; a.npar = d.npar; a.ntmp = d.ntmp; a.nops = d.nops; a.P = P; a.nc = nc; a.d = t->varorder; a.nser = nser;
