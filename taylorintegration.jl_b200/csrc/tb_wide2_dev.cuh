@@ -62,14 +62,16 @@ template <bool FAST> __device__ __forceinline__ double mad2(double a, double b, 
  * table filled once per CTA, q = RN(x y), r = x - q d (exact in one FMA), RN(q + r y) = RN(x / d) (Markstein) when
  * nothing under/overflows; operands outside [2^-767, 2^768) (and 0, Inf, NaN) take the IEEE division.  Same bits. */
 __shared__ double w2_rinv[64];
+/* out of line on purpose: inlined, ptxas if-converts the rare branch and every call pays the whole division */
+__device__ __noinline__ double w2_div_ieee(double a, double b) { return __ddiv_rn(a, b); }
 __device__ __forceinline__ double w2_div_int(double x, int d) {
-    if (d >= 64) return XD(x, (double)d);
+    if (d >= 64) return w2_div_ieee(x, (double)d);
     const double y = w2_rinv[d], dd = (double)d;
     const double q = XM(x, y);
     const double r = __fma_rn(-q, dd, x);
     double q2 = __fma_rn(r, y, q);
     const unsigned e = ((unsigned)__double2hiint(x) & 0x7ff00000u) - 0x10000000u;
-    if (!(e < 0x5ff00000u)) q2 = XD(x, dd);
+    if (!(e < 0x5ff00000u)) q2 = w2_div_ieee(x, dd);
     return q2;
 }
 
@@ -426,6 +428,32 @@ template <bool FAST> __device__ __forceinline__ void wide2_body(const W2Args &a)
             }
             /* stepsize: stepsize.jl:58-99 */
             double h = inf;
+            if (a.reltol == 0.0 && a.abstol >= 0.0) {
+                /* reltol = 0: every candidate is (abstol / |x_c[k]|)^(1/k), decreasing in |x_c[k]|, so the minimum belongs
+                 * to the largest coefficient of each k.  tb_pow errs by < 1 ulp: coefficients more than 2^-40 below the
+                 * maximum cannot win after the 1/k-th power; the ones inside that window are evaluated as well.  Same
+                 * bits as the loop over all components (the path below), two powers per step instead of 2 dof.
+                 * Julia's min propagates NaN (a NaN coefficient, or 0 * Inf from a non-finite |x_c[0]|): tracked apart. */
+                double mk0 = 0.0, mk1 = 0.0;
+                bool bad = false;
+                for (int c = tid; c < a.dof; c += nth) {
+                    const double *X = W + a.xsid[c];
+                    const double a0 = fabs(X[(P - 1) * NS]), a1 = fabs(X[P * NS]);
+                    bad = bad || a0 != a0 || a1 != a1 || ((a0 != 0.0 || a1 != 0.0) && !(fabs(X[0]) < inf));
+                    mk0 = fmax(mk0, a0); mk1 = fmax(mk1, a1);
+                }
+                mk0 = w2_block_reduce(mk0, red, true);
+                mk1 = w2_block_reduce(mk1, red, true);
+                bad = __syncthreads_or(bad);
+                const double th0 = XM(mk0, 0.99999999999909051), th1 = XM(mk1, 0.99999999999909051);
+                for (int c = tid; c < a.dof; c += nth) {
+                    const double *X = W + a.xsid[c];
+                    const double a0 = fabs(X[(P - 1) * NS]), a1 = fabs(X[P * NS]);
+                    if (a0 != 0.0 && (a0 == mk0 || a0 > th0)) h = fmin(h, tb_pow(XD(a.abstol, a0), XD(1.0, (double)(P - 1))));
+                    if (a1 != 0.0 && (a1 == mk1 || a1 > th1)) h = fmin(h, tb_pow(XD(a.abstol, a1), XD(1.0, (double)P)));
+                }
+                if (bad) h = nan;
+            } else
             for (int c = tid; c < a.dof; c += nth) {
                 const double *X = W + a.xsid[c];
                 const double x0norm = fabs(X[0]);
