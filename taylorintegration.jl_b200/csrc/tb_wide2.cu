@@ -30,6 +30,7 @@
 #include <cstdlib>
 #include <cstring>
 #include <map>
+#include <mutex>
 #include <numeric>
 #include <string>
 #include <vector>
@@ -77,6 +78,7 @@ struct Wide2 {
     int gen_ctas = 1, gen_regs = 0, gen_local = 0;
     bool gen_lc_smem = false;
     std::map<int, std::pair<void *, void *>> gen_loaded; /* device -> (module, function) */
+    std::mutex gen_mu;                                   /* guards gen_loaded (calls from several host threads) */
     int device = -1;
     C2Op *d_ops = nullptr;
     double *d_lcc = nullptr;
@@ -588,6 +590,7 @@ int wide2_integrate(Wide2 *w, long long N, const double *q0, const double *param
     const bool gen = !w->gen_cubin.empty();
     void *gen_fn = nullptr;
     if (gen) { /* the specialised kernel: one module per device */
+        std::lock_guard<std::mutex> lk(w->gen_mu);
         auto it = w->gen_loaded.find(dev);
         if (it == w->gen_loaded.end()) {
             void *mod = nullptr, *fn = nullptr;
