@@ -486,7 +486,7 @@ static std::string wide2_generate(const Wide2 *w, bool lc_smem, int ctas, int lc
         {"TB_OP_SUB", TB_OP_SUB}, {"TB_OP_MUL", TB_OP_MUL}, {"TB_OP_DIV", TB_OP_DIV}, {"TB_OP_SQR", TB_OP_SQR},
         {"TB_OP_SQRT", TB_OP_SQRT}, {"TB_OP_POW", TB_OP_POW}, {"TB_OP_EXP", TB_OP_EXP}, {"TB_OP_LOG", TB_OP_LOG},
         {"TB_OP_SINCOS", TB_OP_SINCOS}, {"TB_OP_ZERO", TB_OP_ZERO}, {"TB_OP_ONE", TB_OP_ONE}, {"W_NOP", W_NOP},
-        {"W_LINCOMB", W_LINCOMB}, {"W_SOLCOEFF", W_SOLCOEFF}, {"TB_ST_MAXSTEPS", TB_ST_MAXSTEPS},
+        {"W_LINCOMB", W_LINCOMB}, {"W_SOLCOEFF", W_SOLCOEFF}, {"W_MUL2", W_MUL2}, {"TB_ST_MAXSTEPS", TB_ST_MAXSTEPS},
         {"TB_ST_ZERO_STEP", TB_ST_ZERO_STEP}, {"TB_ST_NONFINITE", TB_ST_NONFINITE}};
     for (auto &kv : ops) { snprintf(buf, sizeof buf, " %s = %d,", kv.first, kv.second); s += buf; }
     s += " TB_W2_ENUM_END };\n";
@@ -500,8 +500,58 @@ static std::string wide2_generate(const Wide2 *w, bool lc_smem, int ctas, int lc
         line("  /* group %zu: %d clusters x %d entries */", g, w->g_count[g], w->g_len[g]);
         if (w->g_count[g] <= w->threads) line("  if (tid < %d) { const int r = tid;", w->g_count[g]);
         else line("  for (int r = tid; r < %d; r += TB_W2_THREADS) {", w->g_count[g]);
+        /* fuse two Cauchy products that share their second operand (many-spin: z_i * S_i and -y_i * S_i) into one
+         * W_MUL2 entry at the place of the first: the later one may move up when no entry in between writes what it
+         * reads or touches what it writes.  Locations compare as (value, shifts-with-rank): equal values, or
+         * persistent ids with different shift behaviour, count as possibly the same series. */
+        const int glen = w->g_len[g];
+        std::vector<int> partner(glen, -1);
+        std::vector<char> skip(glen, 0);
+        if (!getenv("TB_WIDE_NO_MUL2")) {
+            auto E = [&](int j) -> const C2Op & { return w->gops[w->g_off[g] + j]; };
+            auto cauchy = [&](const C2Op &o) { return o.op == TB_OP_MUL && o.a >= 0 && o.b >= 0; };
+            auto same = [&](int va, bool sa, int vb, bool sb) {
+                if (va == -1 || vb == -1) return false;          /* numbers */
+                if (va < 0 || vb < 0) return va == vb;            /* transient slots: per thread, by number */
+                return va == vb || sa != sb;                      /* persistent ids */
+            };
+            for (int p0 = 0; p0 < glen; p0++) {
+                if (skip[p0] || partner[p0] >= 0 || !cauchy(E(p0))) continue;
+                const C2Op &u = E(p0);
+                for (int q = p0 + 1; q < glen; q++) {
+                    const C2Op &v = E(q);
+                    if (skip[q] || !cauchy(v) || v.b != u.b || ((v.flags & 64) != (u.flags & 64)) || ((v.flags & 2) != (u.flags & 2))) continue;
+                    bool ok = !same(v.a, v.flags & 32, u.res, u.flags & 16) && !same(v.res, v.flags & 16, u.res, u.flags & 16);
+                    for (int m = p0 + 1; m < q && ok; m++) {
+                        const C2Op &x = E(m);
+                        if (skip[m]) continue;
+                        const bool xs16 = x.flags & 16, xs128 = x.flags & 128;
+                        /* writes of x: res (and aux for sincos-like entries) against what v reads (a, b) and writes (res) */
+                        const int wr[2] = {x.res, x.aux};
+                        const bool ws[2] = {xs16, xs128};
+                        for (int t = 0; t < 2 && ok; t++) {
+                            if (t == 1 && x.op != TB_OP_SINCOS) break;
+                            if (same(wr[t], ws[t], v.a, v.flags & 32) || same(wr[t], ws[t], v.b, v.flags & 64) ||
+                                same(wr[t], ws[t], v.res, v.flags & 16)) ok = false;
+                        }
+                        if (x.op == W_SOLCOEFF) ok = ok && !same(x.res, xs16, v.a, v.flags & 32) && !same(x.res, xs16, v.b, v.flags & 64);
+                        /* reads of x against v's result; a coupling sum reads persistent series by table */
+                        if (same(x.a, x.flags & 32, v.res, v.flags & 16) || same(x.b, x.flags & 64, v.res, v.flags & 16)) ok = false;
+                        if (x.op == W_LINCOMB && v.res >= 0) ok = false;
+                    }
+                    if (ok) { partner[p0] = q; skip[q] = 1; break; }
+                }
+            }
+        }
         for (int j = 0; j < w->g_len[g]; j++) {
-            const C2Op &o = w->gops[w->g_off[g] + j];
+            if (skip[j]) continue;
+            C2Op o = w->gops[w->g_off[g] + j];
+            if (partner[j] >= 0) { /* second product: a2 -> aux, res2 -> lc_soff, its negation -> bit 2 */
+                const C2Op &v = w->gops[w->g_off[g] + partner[j]];
+                o.op = W_MUL2;
+                o.aux = v.a; o.lc_soff = v.res;
+                o.flags = (o.flags & ~(128 | 256 | 4)) | ((v.flags & 32) ? 128 : 0) | ((v.flags & 16) ? 256 : 0) | ((v.flags & 1) ? 4 : 0);
+            }
             long long no;
             memcpy(&no, &o.immb, sizeof no);
             const bool lit = (o.a == -1 && o.para < 0) || (o.b == -1 && o.parb < 0);

@@ -139,6 +139,28 @@ __device__ __forceinline__ void exec2(const W2Args &A, double *__restrict__ W, d
                 }
             }
             break;
+        case W_MUL2: {
+            /* two Cauchy products with the SAME second operand, fused by wide2_generate (many-spin: z_i * S_i and
+             * -y_i * S_i): S is loaded once and the two dependent add chains interleave.  Each product keeps the
+             * accumulation order of TB_OP_MUL above (same bits).  a2 in o.aux, res2 in o.lc_soff, bit 2: negate a2. */
+            const double *pa = W + o.a, *pc = W + o.aux, *pb = W + o.b + k * NS;
+            const bool bn = (o.flags & 2) != 0;
+            const bool n1 = ((o.flags & 1) != 0) != bn, n2 = ((o.flags & 4) != 0) != bn;
+            const double b0 = pb[0];
+            double r1 = XM(n1 ? -pa[0] : pa[0], b0), r2 = XM(n2 ? -pc[0] : pc[0], b0);
+            for (int i = 1; i <= k; i++) {
+                pa += NS; pc += NS; pb -= NS;
+                const double bb = pb[0];
+                if (FAST) { r1 = fma(n1 ? -pa[0] : pa[0], bb, r1); r2 = fma(n2 ? -pc[0] : pc[0], bb, r2); }
+                else {
+                    const double q1 = XM(pa[0], bb), q2 = XM(pc[0], bb);
+                    r1 = XA(r1, n1 ? -q1 : q1); r2 = XA(r2, n2 ? -q2 : q2);
+                }
+            }
+            if (o.res >= 0) W[k * NS + o.res] = r1; else tr[(-2 - o.res) * TRS] = r1;
+            if (o.lc_soff >= 0) W[k * NS + o.lc_soff] = r2; else tr[(-2 - o.lc_soff) * TRS] = r2;
+            return;
+        }
         case TB_OP_SQR: {
             const double *a = W + o.a;
             if (k == 0) r = XM(a[0], a[0]);

@@ -7,7 +7,7 @@
 
 namespace tbw {
 
-enum { W_NOP = 0, W_LINCOMB = 100, W_SOLCOEFF = 101 };
+enum { W_NOP = 0, W_LINCOMB = 100, W_SOLCOEFF = 101, W_MUL2 = 102 /* generated kernels only: two products sharing operand b */ };
 
 /* internal tape entry: operands are compact series ids (>= 0) or -1 for a number */
 struct WOp {
