@@ -140,6 +140,40 @@ __device__ __forceinline__ double staged_sum(double acc, const TnArgs &a, double
     return acc;
 }
 
+/* sincos! at order k >= 1: ts = sum_i (i A_i) C_{k-i} and tc = sum_i (i A_i) S_{k-i} share the operand (i A_i): ONE
+ * staging per time index (three polynomials per stage, double buffered: the six buffers), one barrier instead of
+ * two, one gather of the shared operand, and the two dependent add chains interleaved.  Each sum keeps its order. */
+template <bool FAST>
+__device__ __forceinline__ void staged_sincos(double &ts, double &tc, const TnArgs &a, const Jets &J, double *__restrict__ stg,
+                                              int m, bool act, int p0, int p1, int oa, int ocos, int osin, int k) {
+    const int nc = a.nc;
+    const unsigned int *__restrict__ pab = a.pair_ab;
+    int buf = 0;
+    if (act) { stg[m] = J.co(oa, 1)[m]; stg[nc + m] = J.co(ocos, k - 1)[m]; stg[2 * nc + m] = J.co(osin, k - 1)[m]; }
+    __syncthreads();
+    for (int i = 1; i <= k; i++) {
+        if (i < k && act) {
+            double *d = stg + (3 * (buf ^ 1)) * nc;
+            d[m] = J.co(oa, i + 1)[m]; d[nc + m] = J.co(ocos, k - i - 1)[m]; d[2 * nc + m] = J.co(osin, k - i - 1)[m];
+        }
+        if (act) {
+            const double *sU = stg + (3 * buf) * nc, *sVc = sU + nc, *sVs = sU + 2 * nc;
+            const bool hf = i >= 2;
+            const double f = (double)i;
+#pragma unroll 2
+            for (int p = p0; p < p1; p++) {
+                const unsigned int ab = pab[p];
+                const double u0 = sU[ab & 0xffffu];
+                const double u = hf ? __dmul_rn(f, u0) : u0;
+                ts = mad<FAST>(u, sVc[ab >> 16], ts);
+                tc = mad<FAST>(u, sVs[ab >> 16], tc);
+            }
+        }
+        __syncthreads();
+        buf ^= 1;
+    }
+}
+
 /* Q = Nn / B over homogeneous degree; nn = Nn[m] in a register.  Q_g = (Nn_g - sum_{j<g} Q_j B_{g-j}) / B_0 */
 template <bool FAST>
 __device__ void tn_div(const TnArgs &a, int m, int degm, double *Q, double nn, const double *B, double *__restrict__ stg) {
@@ -304,11 +338,8 @@ __device__ void run_op(const TnArgs &a, const Jets &J, const double *par, double
             double *Cc = J.co(op.aux, k);
             if (k == 0) tn_sincos<FAST>(a, m, degm, R, Cc, J.co(op.a, 0), stg);
             else {
-                /* two sums over the same scaled operand (i a_i): staged once per sum (same bits, order unchanged) */
-                const double ts = staged_sum<FAST>(0.0, a, stg, m, act, p0, p1, 1, k,
-                    [&](int i, const double *&U, const double *&V, bool &hf, double &f) { U = J.co(op.a, i); V = J.co(op.aux, k - i); hf = i >= 2; f = (double)i; });
-                const double tc = staged_sum<FAST>(0.0, a, stg, m, act, p0, p1, 1, k,
-                    [&](int i, const double *&U, const double *&V, bool &hf, double &f) { U = J.co(op.a, i); V = J.co(op.res, k - i); hf = i >= 2; f = (double)i; });
+                double ts = 0.0, tc = 0.0;
+                staged_sincos<FAST>(ts, tc, a, J, stg, m, act, p0, p1, op.a, op.aux, op.res, k);
                 if (act) { R[m] = __ddiv_rn(ts, (double)k); Cc[m] = __ddiv_rn(-tc, (double)k); }
             }
             break;
