@@ -17,6 +17,7 @@
 
 #include <atomic>
 #include <cstdint>
+#include <cstdlib>
 #include <map>
 #include <mutex>
 #include <string>
@@ -68,6 +69,8 @@ struct TnArgs {
     int *status;
     double *xv_trange; /* [dof x nc x nt x N] */
     unsigned long long *counter;
+    const unsigned int *sched; /* execution schedule of the tape: j | 0xffff0000 = entry j alone, j | q << 16 = the pair (j, q) */
+    int nsched;
 };
 
 template <bool FAST> __device__ __forceinline__ double mad(double a, double b, double c) {
@@ -349,6 +352,125 @@ __device__ void run_op(const TnArgs &a, const Jets &J, const double *par, double
     __syncthreads();
 }
 
+/* ---- two independent tape entries at once ------------------------------------------------------------------
+ * Entries whose time-index sums do not depend on each other (x^2 and y^2, x / r^3 and y / r^3 of kepler1!) run as a
+ * PAIR (host schedule, tn_schedule): one staging of the four operand polynomials per time index, one barrier instead
+ * of two, and the two dependent add chains of a thread interleaved (the same index pairs serve both).  Each sum keeps
+ * its own order and its own finalisation (doubling / division over the homogeneous degrees): same bits.            */
+struct SumDesc { bool has; int oU, oV, ilo, ihi, fmode; double r; };
+
+__device__ __forceinline__ SumDesc sum_desc(const tb_op_t &op, int k) {
+    SumDesc d{false, 0, 0, 0, -1, 0, 0.0};
+    const int ka = TB_OPERAND_KIND(op.a), kb = TB_OPERAND_KIND(op.b);
+    const bool sa = ka == TB_K_PAR || ka == TB_K_IMM, sb = kb == TB_K_PAR || kb == TB_K_IMM;
+    int opc = op.op;
+    if (opc == TB_OP_POW) {
+        if (op.imm == 1.0) opc = TB_OP_IDENTITY;
+        else if (op.imm == 2.0) opc = TB_OP_SQR;
+    }
+    if (opc == TB_OP_MUL && !sa && !sb) { d.has = true; d.oU = op.a; d.oV = op.b; d.ilo = 0; d.ihi = k; }
+    else if (opc == TB_OP_SQR) { const int kodd = k & 1; d.has = true; d.oU = op.a; d.oV = op.a; d.ilo = 0; d.ihi = k == 0 ? 0 : (k - 2 + kodd) / 2; }
+    else if (opc == TB_OP_DIV && !sb) { d.has = true; d.oU = op.res; d.oV = op.b; d.ilo = 0; d.ihi = k - 1; }
+    else if (opc == TB_OP_POW && k > 0) { d.has = true; d.oU = op.res; d.oV = op.a; d.ilo = 0; d.ihi = k - 1; d.fmode = 1; d.r = op.imm; }
+    return d;
+}
+
+/* what run_op does after its time-index sum `acc`; ends with a barrier */
+template <bool FAST>
+__device__ void finish_op(const TnArgs &a, const Jets &J, const double *par, double *scratch, double *stg, const tb_op_t &op, int k,
+                          int m, int degm, double acc) {
+    const int ka = TB_OPERAND_KIND(op.a);
+    const bool sa = ka == TB_K_PAR || ka == TB_K_IMM;
+    const double na = ka == TB_K_PAR ? par[TB_OPERAND_INDEX(op.a)] : op.imm;
+    const bool act = m < a.nc;
+    double *R = J.co(op.res, k);
+    const int p0 = act ? a.pair_off[m] : 0, p1 = act ? a.pair_off[m + 1] : 0;
+    int opc = op.op;
+    if (opc == TB_OP_POW && op.imm == 2.0) opc = TB_OP_SQR;
+    if (opc == TB_OP_MUL) { if (act) R[m] = acc; }
+    else if (opc == TB_OP_SQR) {
+        if (k > 0) {
+            acc = __dmul_rn(2.0, acc);
+            if (!(k & 1)) acc = staged_sum<FAST>(acc, a, stg, m, act, p0, p1, k / 2, k / 2,
+                [&](int i, const double *&U, const double *&V, bool &hf, double &f) { U = J.co(op.a, i); V = J.co(op.a, i); hf = false; f = 0.0; });
+        }
+        if (act) R[m] = acc;
+    } else if (opc == TB_OP_DIV) {
+        double nn = 0.0;
+        if (act) {
+            const double num = sa ? ((k == 0 && m == 0) ? na : 0.0) : J.co(op.a, k)[m];
+            nn = __dsub_rn(num, acc);
+        }
+        tn_div<FAST>(a, m, degm, R, nn, J.co(op.b, 0), stg);
+    } else { /* TB_OP_POW, k > 0 */
+        if (act) scratch[m] = __dmul_rn((double)k, J.co(op.a, 0)[m]);
+        __syncthreads();
+        tn_div<FAST>(a, m, degm, R, acc, scratch, stg);
+    }
+    __syncthreads();
+}
+
+template <bool FAST>
+__device__ void run_pair(const TnArgs &a, const Jets &J, const double *par, double *scratch, double *stg, const tb_op_t &o1,
+                         const tb_op_t &o2, int k, int m, int degm) {
+    const SumDesc d1 = sum_desc(o1, k), d2 = sum_desc(o2, k);
+    if (!d1.has || !d2.has) { /* order 0 of a general power: no sum to share */
+        run_op<FAST>(a, J, par, scratch, stg, o1, k, m, degm);
+        run_op<FAST>(a, J, par, scratch, stg, o2, k, m, degm);
+        return;
+    }
+    const int nc = a.nc;
+    const bool act = m < nc;
+    const int p0 = act ? a.pair_off[m] : 0, p1 = act ? a.pair_off[m + 1] : 0;
+    const unsigned int *__restrict__ pab = a.pair_ab;
+    const int lo = min(d1.ilo, d2.ilo), hi = max(d1.ihi, d2.ihi);
+    double acc1 = 0.0, acc2 = 0.0;
+    auto stage = [&](int i, int buf) {
+        if (!act) return;
+        double *d = stg + (4 * buf) * nc;
+        if (i >= d1.ilo && i <= d1.ihi) { d[m] = J.co(d1.oU, i)[m]; d[nc + m] = J.co(d1.oV, k - i)[m]; }
+        if (i >= d2.ilo && i <= d2.ihi) { d[2 * nc + m] = J.co(d2.oU, i)[m]; d[3 * nc + m] = J.co(d2.oV, k - i)[m]; }
+    };
+    int buf = 0;
+    if (lo <= hi) stage(lo, 0);
+    __syncthreads();
+    for (int i = lo; i <= hi; i++) {
+        if (i < hi) stage(i + 1, buf ^ 1);
+        if (act) {
+            const double *U1 = stg + (4 * buf) * nc, *V1 = U1 + nc, *U2 = U1 + 2 * nc, *V2 = U1 + 3 * nc;
+            const bool in1 = i >= d1.ilo && i <= d1.ihi, in2 = i >= d2.ilo && i <= d2.ihi;
+            const double f1 = d1.fmode ? __dsub_rn(__dmul_rn(d1.r, (double)(k - i)), (double)i) : 0.0;
+            const double f2 = d2.fmode ? __dsub_rn(__dmul_rn(d2.r, (double)(k - i)), (double)i) : 0.0;
+            if (in1 && in2) {
+#pragma unroll 2
+                for (int p = p0; p < p1; p++) {
+                    const unsigned int ab = pab[p];
+                    const int ia = ab & 0xffffu, ib = ab >> 16;
+                    const double u1 = U1[ia], u2 = U2[ia];
+                    acc1 = mad<FAST>(d1.fmode ? __dmul_rn(f1, u1) : u1, V1[ib], acc1);
+                    acc2 = mad<FAST>(d2.fmode ? __dmul_rn(f2, u2) : u2, V2[ib], acc2);
+                }
+            } else if (in1) {
+                for (int p = p0; p < p1; p++) {
+                    const unsigned int ab = pab[p];
+                    const double u1 = U1[ab & 0xffffu];
+                    acc1 = mad<FAST>(d1.fmode ? __dmul_rn(f1, u1) : u1, V1[ab >> 16], acc1);
+                }
+            } else if (in2) {
+                for (int p = p0; p < p1; p++) {
+                    const unsigned int ab = pab[p];
+                    const double u2 = U2[ab & 0xffffu];
+                    acc2 = mad<FAST>(d2.fmode ? __dmul_rn(f2, u2) : u2, V2[ab >> 16], acc2);
+                }
+            }
+        }
+        __syncthreads();
+        buf ^= 1;
+    }
+    finish_op<FAST>(a, J, par, scratch, stg, o1, k, m, degm, acc1);
+    finish_op<FAST>(a, J, par, scratch, stg, o2, k, m, degm, acc2);
+}
+
 /* block-wide max of |v| (order-independent, so bit-identical to the oracle's sequential _norminf) */
 __device__ double block_max(double v, double *red) {
     for (int o = 16; o > 0; o >>= 1) v = fmax(v, __shfl_xor_sync(0xffffffffu, v, o));
@@ -364,11 +486,11 @@ __device__ double block_max(double v, double *red) {
 template <bool FAST> __global__ void __launch_bounds__(1024) tn_kernel(const TnArgs a_in) {
     __shared__ double red[32];
     __shared__ unsigned long long s_idx;
-    extern __shared__ double scratch[]; /* [nc] + staging buffers [6][nc] (+ the pair table) */
+    extern __shared__ double scratch[]; /* [nc] + staging buffers [8][nc] (+ the pair table) */
     TnArgs a = a_in;
     double *stg = scratch + a.nc;
     if (a.pairs_in_smem) { /* the index pairs are read once per product term: keep them next to the operands */
-        unsigned int *sp = (unsigned int *)(scratch + 7 * a.nc);
+        unsigned int *sp = (unsigned int *)(scratch + 9 * a.nc);
         for (int q = threadIdx.x; q < a.npairs; q += blockDim.x) sp[q] = a_in.pair_ab[q];
         a.pair_ab = sp;
         __syncthreads();
@@ -409,7 +531,12 @@ template <bool FAST> __global__ void __launch_bounds__(1024) tn_kernel(const TnA
             if (m == 0) J.co(TIME, 0)[0] = t0;
             __syncthreads();
             for (int k = 0; k < P; k++) {
-                for (int j = 0; j < a.nops; j++) run_op<FAST>(a, J, par, scratch, stg, a.ops[j], k, m, degm);
+                for (int s = 0; s < a.nsched; s++) {
+                    const unsigned int e = a.sched[s];
+                    const int j = e & 0xffffu, q = e >> 16;
+                    if (q == 0xffff) run_op<FAST>(a, J, par, scratch, stg, a.ops[j], k, m, degm);
+                    else run_pair<FAST>(a, J, par, scratch, stg, a.ops[j], a.ops[q], k, m, degm);
+                }
                 if (act)
                     for (int c = 0; c < a.dof; c++)
                         J.co(TB_OPERAND(TB_K_X, c), k + 1)[m] = __ddiv_rn(J.co(TB_OPERAND(TB_K_DX, c), k)[m], (double)(k + 1));
@@ -516,8 +643,55 @@ struct tb_tn {
     int *d_off = nullptr;
     unsigned short *d_pa = nullptr, *d_pb = nullptr;
     unsigned int *d_pab = nullptr;
+    unsigned int *d_sched = nullptr;
+    std::vector<unsigned int> sched; /* execution schedule (tn_schedule) */
     unsigned long long serial = 0; /* identity of this handle (tb_tn_integrate_static: whose tables sit in the static array) */
 };
+
+/* Execution schedule of the tape: entries in tape order, except that an entry with a time-index sum (series x series
+ * product, square, power, series / series) is PAIRED with the next such entry that does not read its result; the
+ * entries between the two move in front of the pair (they cannot depend on the first either, or the pair is not
+ * formed).  Temporaries and dx are written once (the tracer is SSA), so moving independent entries is safe.
+ * TB_TN_NO_PAIRS=1 keeps the plain tape order.                                                                    */
+static void tn_schedule(tb_tn *t) {
+    const tb_ode_desc_t &d = t->ode.desc;
+    const std::vector<tb_op_t> &ops = t->ode.ops;
+    auto numeric = [](int32_t o) { const int k = TB_OPERAND_KIND(o); return k == TB_K_PAR || k == TB_K_IMM; };
+    auto summing = [&](const tb_op_t &o) {
+        if (o.op == TB_OP_MUL) return !numeric(o.a) && !numeric(o.b);
+        if (o.op == TB_OP_SQR) return true;
+        if (o.op == TB_OP_POW) return o.imm != 1.0;
+        if (o.op == TB_OP_DIV) return !numeric(o.b);
+        return false;
+    };
+    auto reads = [&](const tb_op_t &o, int32_t loc) { return o.a == loc || o.b == loc; };
+    std::vector<char> done(d.nops, 0);
+    t->sched.clear();
+    const bool pairs = !getenv("TB_TN_NO_PAIRS");
+    for (int j = 0; j < d.nops; j++) {
+        if (done[j]) continue;
+        int q = -1;
+        if (pairs && summing(ops[j])) {
+            bool blocked = false;
+            for (int c = j + 1; c < d.nops && !blocked; c++) {
+                if (done[c]) continue;
+                const bool dep = reads(ops[c], ops[j].res) || (ops[j].op == TB_OP_SINCOS && reads(ops[c], ops[j].aux));
+                if (dep) { blocked = true; break; } /* everything after a dependent entry stays behind the pair */
+                if (summing(ops[c])) { q = c; break; }
+                if (ops[c].op == TB_OP_SINCOS) { blocked = true; break; } /* keep the (internally fused) sincos! in place */
+            }
+        }
+        if (q >= 0) {
+            for (int c = j + 1; c < q; c++)
+                if (!done[c]) { t->sched.push_back((unsigned int)c | 0xffff0000u); done[c] = 1; }
+            t->sched.push_back((unsigned int)j | ((unsigned int)q << 16));
+            done[j] = done[q] = 1;
+        } else {
+            t->sched.push_back((unsigned int)j | 0xffff0000u);
+            done[j] = 1;
+        }
+    }
+}
 
 extern "C" {
 
@@ -546,6 +720,7 @@ tb_tn_t *tb_tn_create(const tb_ode_t *ode, int order, int nvars, int varorder, i
     t->order = order; t->nvars = nvars; t->varorder = varorder; t->mode = mode;
     t->T = tbtn::make_tables(nvars, varorder);
     if (t->T.ncoef > 1024) { tb::set_error("tb_tn_create: more than 1024 polynomial coefficients"); delete t; return nullptr; }
+    tn_schedule(t);
     static std::atomic<unsigned long long> next_serial{1};
     t->serial = next_serial++;
     return t;
@@ -553,7 +728,7 @@ tb_tn_t *tb_tn_create(const tb_ode_t *ode, int order, int nvars, int varorder, i
 
 void tb_tn_free(tb_tn_t *t) {
     if (!t) return;
-    if (t->d_ops) { cudaFree(t->d_ops); cudaFree(t->d_deg); cudaFree(t->d_off); cudaFree(t->d_pa); cudaFree(t->d_pb); cudaFree(t->d_pab); }
+    if (t->d_ops) { cudaFree(t->d_ops); cudaFree(t->d_deg); cudaFree(t->d_off); cudaFree(t->d_pa); cudaFree(t->d_pb); cudaFree(t->d_pab); cudaFree(t->d_sched); }
     delete t;
 }
 
@@ -590,9 +765,11 @@ int tb_tn_integrate(tb_tn_t *t, int64_t N, const double *q0, const double *param
         for (size_t q = 0; q < np; q++) pab[q] = (unsigned int)t->T.pair_a[q] | ((unsigned int)t->T.pair_b[q] << 16);
         TB_CUDA(cudaMalloc(&t->d_pab, 4 * (np ? np : 1)));
         TB_CUDA(cudaMemcpy(t->d_pab, pab.data(), 4 * np, cudaMemcpyHostToDevice));
+        TB_CUDA(cudaMalloc(&t->d_sched, 4 * (t->sched.size() ? t->sched.size() : 1)));
+        TB_CUDA(cudaMemcpy(t->d_sched, t->sched.data(), 4 * t->sched.size(), cudaMemcpyHostToDevice));
     }
     const int threads = ((nc + 31) / 32) * 32;
-    size_t smem = sizeof(double) * nc * 7; /* scratch + 6 staging buffers */
+    size_t smem = sizeof(double) * nc * 9; /* scratch + 8 staging buffers */
     const size_t npairs = t->T.pair_a.size();
     const bool pairs_in_smem = smem + 4 * npairs <= 100 * 1024;
     if (pairs_in_smem) smem += 4 * npairs;
@@ -610,7 +787,7 @@ int tb_tn_integrate(tb_tn_t *t, int64_t N, const double *q0, const double *param
     TnArgs a{};
     a.N = N; a.dof = d.dof; a.npar = d.npar; a.ntmp = d.ntmp; a.nops = d.nops; a.P = P; a.nc = nc; a.d = t->varorder;
     a.nser = 2 * d.dof + d.ntmp + 1;
-    a.ops = t->d_ops; a.deg = t->d_deg; a.pair_off = t->d_off; a.pair_a = t->d_pa; a.pair_b = t->d_pb; a.pair_ab = t->d_pab; a.npairs = (int)npairs; a.pairs_in_smem = pairs_in_smem ? 1 : 0;
+    a.ops = t->d_ops; a.deg = t->d_deg; a.pair_off = t->d_off; a.pair_a = t->d_pa; a.pair_b = t->d_pb; a.pair_ab = t->d_pab; a.sched = t->d_sched; a.nsched = (int)t->sched.size(); a.npairs = (int)npairs; a.pairs_in_smem = pairs_in_smem ? 1 : 0;
     a.nt = trange ? nt : 0; a.t0 = t0; a.tmax = tmax; a.abstol = o->abstol; a.reltol = o->reltol;
     a.minstep = o->minstepsize; a.maxstep = o->maxstepsize; a.maxsteps = o->maxsteps; a.params_per_traj = o->params_per_traj;
     const size_t nq = (size_t)d.dof * nc * N, npar = (size_t)(d.npar > 0 ? d.npar : 1) * (o->params_per_traj ? N : 1);
@@ -717,7 +894,7 @@ extern "C" int tb_tn_integrate_static(tb_tn_t *t, int64_t N, const double *d_q0,
     const int nc = t->T.ncoef, P = t->order;
     const size_t np = t->T.pair_a.size();
     const int threads = ((nc + 31) / 32) * 32;
-    size_t smem = sizeof(double) * nc * 7;
+    size_t smem = sizeof(double) * nc * 9;
     const bool pairs_in_smem = smem + 4 * np <= 100 * 1024;
     if (pairs_in_smem) smem += 4 * np;
     const bool fast = t->mode == TB_MODE_FAST;
@@ -732,7 +909,7 @@ extern "C" int tb_tn_integrate_static(tb_tn_t *t, int64_t N, const double *d_q0,
     const int nser = 2 * d.dof + d.ntmp + 1;
     const size_t o_ctr = 0, o_ops = 256, o_deg = o_ops + up(sizeof(tb_op_t) * (size_t)d.nops), o_off = o_deg + up((size_t)nc),
                  o_pab = o_off + up(sizeof(int) * (size_t)(nc + 1)), o_pa = o_pab + up(4 * np), o_pb = o_pa + up(2 * np),
-                 o_work = o_pb + up(2 * np);
+                 o_sch = o_pb + up(2 * np), o_work = o_sch + up(4 * t->sched.size());
     const size_t per_block = sizeof(double) * (size_t)nser * (size_t)(P + 1) * (size_t)nc;
     if (o_work + per_block > (size_t)TB_TN_STATIC_SCRATCH_BYTES) {
         tb::set_error("tb_tn_integrate_static: one trajectory needs " + std::to_string(o_work + per_block) +
@@ -771,12 +948,14 @@ extern "C" int tb_tn_integrate_static(tb_tn_t *t, int64_t N, const double *d_q0,
             TB_CUDA(cudaMemcpyAsync(base + o_pa, t->T.pair_a.data(), 2 * np, cudaMemcpyHostToDevice, st));
             TB_CUDA(cudaMemcpyAsync(base + o_pb, t->T.pair_b.data(), 2 * np, cudaMemcpyHostToDevice, st));
         }
+        if (!t->sched.empty()) TB_CUDA(cudaMemcpyAsync(base + o_sch, t->sched.data(), 4 * t->sched.size(), cudaMemcpyHostToDevice, st));
     }
     TnArgs a{};
     a.N = N; a.dof = d.dof; a.npar = d.npar; a.ntmp = d.ntmp; a.nops = d.nops; a.P = P; a.nc = nc; a.d = t->varorder; a.nser = nser;
     a.ops = (const tb_op_t *)(base + o_ops); a.deg = base + o_deg; a.pair_off = (const int *)(base + o_off);
     a.pair_a = (const unsigned short *)(base + o_pa); a.pair_b = (const unsigned short *)(base + o_pb);
-    a.pair_ab = (const unsigned int *)(base + o_pab); a.npairs = (int)np; a.pairs_in_smem = pairs_in_smem ? 1 : 0;
+    a.pair_ab = (const unsigned int *)(base + o_pab); a.npairs = (int)np;
+    a.sched = (const unsigned int *)(base + o_sch); a.nsched = (int)t->sched.size(); a.pairs_in_smem = pairs_in_smem ? 1 : 0;
     a.q0 = d_q0; a.params = d_params; a.trange = d_trange; a.nt = d_trange ? nt : 0; a.t0 = t0; a.tmax = tmax;
     a.abstol = o->abstol; a.reltol = o->reltol; a.minstep = o->minstepsize; a.maxstep = o->maxstepsize; a.maxsteps = o->maxsteps;
     a.params_per_traj = o->params_per_traj;
