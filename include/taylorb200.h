@@ -362,6 +362,10 @@ typedef struct tb_tn_out {
 tb_tn_t *tb_tn_create(const tb_ode_t *ode, int order, int nvars, int varorder, int mode);
 void tb_tn_free(tb_tn_t *t);
 int tb_tn_ncoef(const tb_tn_t *t);
+/* The kernel runs independent tape entries with a time-index sum (products, squares, powers, divisions) as PAIRS:
+ * entry of the schedule = j | 0xffff0000 (tape entry j alone) or j | q << 16 (entries j and q together; the entries
+ * between them were moved ahead).  Returns the number of schedule entries, writes at most `cap`.  For inspection. */
+int tb_tn_schedule(const tb_tn_t *t, uint32_t *sched, int cap);
 /* exponents [ncoef x nvars] of the flat coefficient order; returns ncoef        */
 int tb_tn_monomials(const tb_tn_t *t, int32_t *expo);
 /* HOST buffers. trange == NULL: (t0,tmax) driver (taylorinteg.jl:329-381); else the

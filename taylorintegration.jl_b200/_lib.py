@@ -91,7 +91,7 @@ EXPORTS = [
     "tb_generate_source", "tb_compile", "tb_integrate_multi", "tb_wide_layout", "tb_wide_generated", "tb_wide_source", "tb_wide_log", "tb_dense_eval_device", "tb_serialize_device", "tb_kernel_free", "tb_kernel_source", "tb_kernel_log", "tb_kernel_info",
     "tb_kernel_cubin", "tb_integrate", "tb_integrate_trange", "tb_work_bytes", "tb_integrate_device",
     "tb_launch_count", "tb_jet", "tb_dense_eval", "tb_fp64_peak", "tb_device_count", "tb_set_device",
-    "tb_tn_create", "tb_tn_free", "tb_tn_ncoef", "tb_tn_monomials", "tb_tn_integrate", "tb_tn_integrate_static",
+    "tb_tn_create", "tb_tn_free", "tb_tn_ncoef", "tb_tn_monomials", "tb_tn_schedule", "tb_tn_integrate", "tb_tn_integrate_static",
     "tb_wide_create", "tb_wide_free", "tb_wide_info", "tb_wide_integrate", "tb_last_kernel_ms",
 ]
 
@@ -157,6 +157,7 @@ def lib() -> C.CDLL:
     L.tb_tn_free.argtypes = [vp]
     L.tb_tn_ncoef.argtypes = [vp]
     L.tb_tn_monomials.argtypes = [vp, vp]
+    L.tb_tn_schedule.argtypes = [vp, vp, C.c_int]
     L.tb_tn_integrate.argtypes = [vp, C.c_int64, vp, vp, C.c_double, C.c_double, vp, C.c_int64, C.POINTER(TbOpts),
                                   C.POINTER(TbTnOut)]
     L.tb_tn_integrate_static.argtypes = [vp, C.c_int64, vp, vp, C.c_double, C.c_double, vp, C.c_int64, C.POINTER(TbOpts),

@@ -734,6 +734,14 @@ void tb_tn_free(tb_tn_t *t) {
 
 int tb_tn_ncoef(const tb_tn_t *t) { return t ? t->T.ncoef : TB_ERR_ARG; }
 
+/* execution schedule of the tape (tn_schedule): entry = j | 0xffff0000 (tape entry j alone) or j | q << 16 (the
+ * entries j and q as a pair); returns the number of entries, writes at most `cap` of them */
+int tb_tn_schedule(const tb_tn_t *t, uint32_t *sched, int cap) {
+    if (!t) return TB_ERR_ARG;
+    for (int i = 0; i < cap && i < (int)t->sched.size(); i++) sched[i] = t->sched[i];
+    return (int)t->sched.size();
+}
+
 int tb_tn_monomials(const tb_tn_t *t, int32_t *expo) {
     if (!t || !expo) return TB_ERR_ARG;
     for (size_t i = 0; i < t->T.expo.size(); i++) expo[i] = t->T.expo[i];

@@ -173,3 +173,20 @@ def test_gpu_kepler_4vars_order8_config5b_bitwise():
     xi = np.array([1e-3, -2e-3, 1.5e-3, -0.5e-3])
     disp = tb.taylorinteg(tape, q + xi[:, None], 0.0, tmax, 28, 1e-20, mu, maxsteps=2000)
     assert np.allclose(sol.evaluate(xi)[:, :2], disp.xfinal[:, :2], rtol=0, atol=1e-10)  # e = 0.9 needs |xi| smaller
+
+
+def test_schedule_pairs_independent_entries():
+    """tn_schedule: kepler1! = [x^2 | y^2], +, ^1.5, identity x2, mu*x, mu*y moved ahead, [x/r^3 | y/r^3]; the
+    pendulum's sincos! stays alone (it fuses its two sums internally)."""
+    import ctypes as C
+    from taylorintegration_b200 import _lib as L
+
+    def sched(jt):
+        buf = (C.c_uint32 * 64)()
+        n = L.lib().tb_tn_schedule(jt._t, buf, 64)
+        return [(e & 0xffff, None if (e >> 16) == 0xffff else e >> 16) for e in list(buf)[:n]]
+
+    k = sched(tb.JetTransport(P.kepler_tape(), 28, 2, 2))
+    assert k == [(0, 1), (2, None), (3, None), (4, None), (5, None), (6, None), (8, None), (7, 9)]
+    p = sched(tb.JetTransport(P.pendulum_tape(events=False), 25, 2, 2))
+    assert all(q is None for _, q in p) and [j for j, _ in p] == list(range(len(p)))

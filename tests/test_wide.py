@@ -95,6 +95,9 @@ def test_cluster_layout_of_the_shared_memory_kernel():
     wk = api.WideKernel(P.manyspin_tape(100), 25)
     assert info["generated"] == 1 and info["local_bytes"] == 0 and info["coupling_in_smem"] == 0
     assert "tb_w2_groups" in wk.source and "tb_w2_kernel" in wk.log
+    # the two Cauchy products of a spin (z_i * S_i, -y_i * S_i) share S_i: fused into one W_MUL2 entry (op 102), the
+    # second product moved up past the one-term coupling entry that does not touch it
+    assert wk.source.count("o.op = 102;") == 1 and wk.source.count("o.op = 5;") == 1  # 5: the scalar * series of group 1
     k = api.WideKernel(P.kepler_tape(), 28).info()   # one cluster: everything depends on r^3
     assert k["threads"] == 32 and k["stored_series"] >= 8
 
