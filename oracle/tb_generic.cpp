@@ -172,9 +172,30 @@ void harmonic(std::vector<T1> &dx, const std::vector<T1> &x, const double *p, co
     dx[1] = -((p[0] * p[0]) * x[0]);
 }
 
+/* benchmark/manyspin_benchmarks.jl:10-41 (spin_odes!) with nn = 5; params = [B[1..5], J[a, i] at 5 + a*5 + i] */
+void spin5(std::vector<T1> &dq, const std::vector<T1> &q, const double *p, const T1 &) {
+    const int nn = 5;
+    const double *B = p, *J = p + nn;
+    std::vector<T1> x(nn), y(nn), z(nn), sum_s(nn), aux(nn);
+    for (int i = 0; i < nn; i++) { x[i] = q[3 * i]; y[i] = q[3 * i + 1]; z[i] = q[3 * i + 2]; }
+    T1 zz(x[0].order()); /* zero(x[1]) */
+    for (int i = 0; i < nn; i++) {
+        sum_s[i] = zz;
+        for (int a = 0; a < nn; a++) {
+            aux[i] = sum_s[i];
+            T1 xJ = J[a * nn + i] * x[a];
+            sum_s[i] = aux[i] + xJ;
+        }
+        dq[3 * i] = (-B[i]) * y[i];
+        dq[3 * i + 1] = B[i] * x[i] + z[i] * sum_s[i];
+        dq[3 * i + 2] = (-y[i]) * sum_s[i];
+    }
+}
+
 struct Problem { const char *name; int dof; Rhs f; };
 const Problem PROBLEMS[] = {{"kepler1!", 4, kepler1}, {"pendulum!", 2, pendulum}, {"lorenz!", 3, lorenz},
-                            {"xsquared", 1, xsquared}, {"cos_t", 1, cos_t}, {"harmonic", 2, harmonic}};
+                            {"xsquared", 1, xsquared}, {"cos_t", 1, cos_t}, {"harmonic", 2, harmonic},
+                            {"spin_odes!5", 15, spin5}};
 const int NPROBLEMS = (int)(sizeof(PROBLEMS) / sizeof(PROBLEMS[0]));
 
 /* jetcoeffs!(eqsdiff!, t, x, dx, xaux, params): src/integrator/jetcoeffs.jl:66-92 */

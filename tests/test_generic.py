@@ -68,3 +68,22 @@ def test_harmonic_oscillator_scalar_times_series():
     (tg, xg, _), (tp, xp, _) = _both("harmonic", tape, 20, np.array([1.0, 0.0]), 0.0, 300.0, np.array([2.0]), maxsteps=1000)
     assert np.array_equal(tg, tp) and np.array_equal(xg, xp)
     assert abs(xg[0, -1] - np.cos(600.0)) < 1e-12 and abs(xg[1, -1] + 2 * np.sin(600.0)) < 3e-12
+
+
+def test_manyspin5_generic_equals_parsed_bitwise():
+    # benchmark/manyspin_benchmarks.jl:10-41 with 5 spins (the reference benchmarks 3..7): the coupling loops
+    # `sum_s[i] = aux[i] + J[a,i]*x[a]` written out on Taylor1 values against the tape the tracer produces
+    nn = 5
+    B, J = P.fix_B(nn), P.fix_J(nn)
+    tape = P.manyspin_tape(nn, B, J)
+    q0 = P.manyspin_ensemble(nn, 3)[:, 1].copy()
+    par = np.concatenate([B, J.reshape(-1)])  # J[a, i] at 5 + a*5 + i
+    xg = oracle.generic_jet("spin_odes!5", 25, q0, par)
+    xp, _, _ = oracle.jet(tape, 25, q0)
+    assert np.array_equal(xg, xp)
+    tg, xgi, _ = oracle.generic_integrate("spin_odes!5", 25, q0, 0.0, 10.0, par, maxsteps=2000)
+    s = oracle.integrate(tape, 25, q0, 0.0, 10.0, steps=True, maxsteps=2000)
+    n = int(s.nsteps[0])
+    assert len(tg) == n + 1 and np.array_equal(tg, s.t[: n + 1, 0]) and np.array_equal(xgi, s.x[:, : n + 1, 0])
+    # |s_i| = 1 is conserved by the equations of motion
+    assert np.allclose((xgi[:, -1].reshape(nn, 3) ** 2).sum(1), 1.0, atol=1e-12)
