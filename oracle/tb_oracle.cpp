@@ -825,6 +825,9 @@ void parallel_for(int64_t N, int nthreads, F f) {
 
 extern "C" {
 
+/* modifiedGS! on one column-major n x n matrix (tests: the properties test/lyapunov.jl:88-110 asks of the QR step) */
+void tbo_modified_gs(const double *A, double *Q, double *R, int n) { modifiedGS(A, Q, R, n); }
+
 /* accuracy probes for tests/test_math.py */
 double tbo_math_pow(double x, double y) { return tb_pow(x, y); }
 void tbo_math_pow_pair(double x1, double y1, double x2, double y2, double *r) { tb_pair p = tb_pow_pair(x1, y1, x2, y2); r[0] = p.a; r[1] = p.b; }

@@ -94,3 +94,22 @@ def test_monomial_order_is_pinned_by_an_asymmetric_displacement():
     swapped = evaluate(r["xfinal"], mon[:, ::-1], xi)[:, 0]
     assert np.max(np.abs(good - s2.xfinal[:, 0])) < 1e-11
     assert np.max(np.abs(swapped - s2.xfinal[:, 0])) > 1e-5
+
+
+def test_modified_gram_schmidt_has_the_properties_the_reference_tests():
+    """test/lyapunov.jl:88-110 (stated there for classicalGS!, the same contract holds for the modifiedGS! the
+    integrator calls, src/lyapunovspectrum.jl:118-146): A = QR to 1e-14, orthonormal columns, R upper triangular with
+    a positive diagonal."""
+    import ctypes as C
+    lib = oracle.lib()
+    lib.tbo_modified_gs.argtypes = [C.c_void_p, C.c_void_p, C.c_void_p, C.c_int]
+    lib.tbo_modified_gs.restype = None
+    rng = np.random.Generator(np.random.PCG64(7))
+    for n in (2, 3, 6):
+        A = np.asfortranarray(rng.random((n, n)))
+        Q, R = np.zeros((n, n), order="F"), np.zeros((n, n), order="F")
+        lib.tbo_modified_gs(A.ctypes.data, Q.ctypes.data, R.ctypes.data, n)
+        assert np.abs(A - Q @ R).max() < 1e-14
+        assert np.allclose(np.diag(Q.T @ Q), 1.0, rtol=0, atol=1e-14)
+        assert np.abs(Q.T @ Q - np.eye(n)).max() < 1e-10
+        assert np.array_equal(R, np.triu(R)) and np.all(np.diag(R) > 0)
