@@ -192,10 +192,29 @@ void spin5(std::vector<T1> &dq, const std::vector<T1> &q, const double *p, const
     }
 }
 
+/* test/taylorize.jl:1488-1500: the Kepler problem "using sqrt", r = sqrt(q1^2 + q2^2), r^3, mu = -1 a local */
+void kepler_sqrt(std::vector<T1> &dq, const std::vector<T1> &q, const double *, const T1 &) {
+    const double mu = -1.0;
+    T1 r = sqrt_(pow_(q[0], 2.0) + pow_(q[1], 2.0));
+    T1 r_p3d2 = pow_(r, 3.0);
+    dq[0] = q[2];
+    dq[1] = q[3];
+    dq[2] = (mu * q[0]) / r_p3d2;
+    dq[3] = (mu * q[1]) / r_p3d2;
+}
+/* test/taylorize.jl:999-1005 (multpendula1!): 3 uncoupled pendula written as a loop */
+void multpendula3(std::vector<T1> &dx, const std::vector<T1> &x, const double *, const T1 &) {
+    const int nn = 3;
+    for (int i = 0; i < nn; i++) {
+        dx[i] = x[nn + i];
+        dx[i + nn] = -sin_(x[i]);
+    }
+}
+
 struct Problem { const char *name; int dof; Rhs f; };
 const Problem PROBLEMS[] = {{"kepler1!", 4, kepler1}, {"pendulum!", 2, pendulum}, {"lorenz!", 3, lorenz},
                             {"xsquared", 1, xsquared}, {"cos_t", 1, cos_t}, {"harmonic", 2, harmonic},
-                            {"spin_odes!5", 15, spin5}};
+                            {"spin_odes!5", 15, spin5}, {"kepler_sqrt!", 4, kepler_sqrt}, {"multpendula!", 6, multpendula3}};
 const int NPROBLEMS = (int)(sizeof(PROBLEMS) / sizeof(PROBLEMS[0]));
 
 /* jetcoeffs!(eqsdiff!, t, x, dx, xaux, params): src/integrator/jetcoeffs.jl:66-92 */

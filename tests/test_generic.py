@@ -87,3 +87,29 @@ def test_manyspin5_generic_equals_parsed_bitwise():
     assert len(tg) == n + 1 and np.array_equal(tg, s.t[: n + 1, 0]) and np.array_equal(xgi, s.x[:, : n + 1, 0])
     # |s_i| = 1 is conserved by the equations of motion
     assert np.allclose((xgi[:, -1].reshape(nn, 3) ** 2).sum(1), 1.0, atol=1e-12)
+
+
+def test_kepler_with_sqrt_and_looped_pendula_generic_equals_parsed_bitwise():
+    # test/taylorize.jl:1488-1500 (r = sqrt(q1^2 + q2^2), r^3) and 999-1005 (pendula in a loop): sqrt!, an integer
+    # power through pow!, and a RHS written with a loop, against the traced tapes
+    from taylorintegration_b200.tape import sqrt, sin
+
+    def kep(dq, q, p, t):
+        mu = -1.0
+        r = sqrt(q[0] ** 2 + q[1] ** 2)
+        r3 = r ** 3
+        dq[0] = q[2]
+        dq[1] = q[3]
+        dq[2] = mu * q[0] / r3
+        dq[3] = mu * q[1] / r3
+    q0 = np.array([0.2, 0.0, 0.0, 3.0])
+    (tg, xg, _), (tp, xp, _) = _both("kepler_sqrt!", tb.taylorize(kep, 4, 0), 28, q0, 0.0, 2 * np.pi * 10, maxsteps=5000)
+    assert np.array_equal(tg, tp) and np.array_equal(xg, xp) and len(tg) > 400
+
+    def pend(dx, x, p, t):
+        for i in range(3):
+            dx[i] = x[3 + i]
+            dx[i + 3] = -sin(x[i])
+    q0 = np.array([1.3, 0.4, 2.9, 0.0, 0.5, -0.2])
+    (tg, xg, _), (tp, xp, _) = _both("multpendula!", tb.taylorize(pend, 6, 0), 25, q0, 0.0, 40.0, maxsteps=3000)
+    assert np.array_equal(tg, tp) and np.array_equal(xg, xp)
