@@ -210,3 +210,121 @@ def jetcoeffs(f, q0, params, t0, order):
             dj = d.c[o] if isinstance(d, T1) else (float(d) if o == 0 else 0.0)
             x[j][o + 1] = dj / (o + 1)
     return x
+
+
+# ---- primitives with an auxiliary series (src/parse_eqs.jl:1013-1046; recurrences as oracle/tb_oracle.cpp p_tan ...) ----
+def _m1(name, x):
+    f = getattr(_m(), name)
+    f.argtypes = [C.c_double]
+    f.restype = C.c_double
+    return f(x)
+
+
+def _sqr_k(a, k):
+    """coefficient k of a^2 (sqr!)"""
+    if k == 0:
+        return a[0] * a[0]
+    kodd = k % 2
+    kend = (k - 2 + kodd) // 2
+    s = a[0] * a[k]
+    for i in range(1, kend + 1):
+        s += a[i] * a[k - i]
+    s = 2 * s
+    if kodd == 0:
+        s += a[k // 2] * a[k // 2]
+    return s
+
+
+def _tan(x, hyp):
+    a = x.c
+    c = [_m1("tbo_math_tanh" if hyp else "tbo_math_tan", a[0])]
+    c2 = [c[0] * c[0]]
+    for k in range(1, len(a)):
+        s = k * a[k] * c2[0]
+        for i in range(1, k):
+            s += (k - i) * a[k - i] * c2[i]
+        c.append(a[k] - s / k if hyp else a[k] + s / k)
+        c2.append(_sqr_k(c, k))
+    return T1(c)
+
+
+def tan(x):
+    return _tan(x, False)
+
+
+def tanh(x):
+    return _tan(x, True)
+
+
+def sinhcosh(x):
+    a = x.c
+    s0, c0 = C.c_double(), C.c_double()
+    f = _m().tbo_math_sinhcosh
+    f.argtypes = [C.c_double, C.POINTER(C.c_double), C.POINTER(C.c_double)]
+    f.restype = None
+    f(a[0], C.byref(s0), C.byref(c0))
+    s, c = [s0.value], [c0.value]
+    for k in range(1, len(a)):
+        xx = a[1]
+        sk, ck = xx * c[k - 1], xx * s[k - 1]
+        for i in range(2, k + 1):
+            xx = i * a[i]
+            sk += xx * c[k - i]
+            ck += xx * s[k - i]
+        s.append(sk / k)
+        c.append(ck / k)
+    return T1(s), T1(c)
+
+
+def sinh(x):
+    return sinhcosh(x)[0]
+
+
+def cosh(x):
+    return sinhcosh(x)[1]
+
+
+def atan(x):
+    a = x.c
+    c, r = [_m1("tbo_math_atan", a[0])], [1 + a[0] * a[0]]
+    for k in range(1, len(a)):
+        s = 0.0
+        if k >= 2:
+            s = (k - 1) * r[1] * c[k - 1]
+            for i in range(2, k):
+                s += (k - i) * r[i] * c[k - i]
+        r.append(_sqr_k(a, k))
+        c.append((a[k] - s / k) / r[0])
+    return T1(c)
+
+
+def _asin(x, is_acos):
+    a = x.c
+    c = [_m1("tbo_math_acos" if is_acos else "tbo_math_asin", a[0])]
+    r = [math.sqrt(1 - a[0] * a[0])]
+    for k in range(1, len(a)):
+        s = 0.0
+        if k >= 2:
+            s = (k - 1) * r[1] * c[k - 1]
+            for i in range(2, k):
+                s += (k - i) * r[i] * c[k - i]
+        ak = -_sqr_k(a, k)
+        kodd = k % 2
+        kend = (k - 2 + kodd) // 2
+        q = 0.0
+        for i in range(1, kend + 1):
+            q = r[i] * r[k - i] if i == 1 else q + r[i] * r[k - i]
+        aux = ak - 2 * q
+        if kodd == 0:
+            aux -= r[kend + 1] * r[kend + 1]
+        r.append(aux / (2 * r[0]))
+        c.append(-(a[k] + s / k) / r[0] if is_acos else (a[k] - s / k) / r[0])
+    return T1(c)
+
+
+def asin(x):
+    return _asin(x, False)
+
+
+def acos(x):
+    return _asin(x, True)

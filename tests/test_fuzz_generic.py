@@ -12,7 +12,8 @@ import pygeneric as G
 import taylorintegration_b200 as tb
 from taylorintegration_b200 import tape as TP
 
-UN = ("sin", "cos", "exp_b", "sqrt_p", "log_p", "pow15_p", "sq", "cube", "neg")
+UN = ("sin", "cos", "exp_b", "sqrt_p", "log_p", "pow15_p", "sq", "cube", "neg",
+      "tan_b", "tanh", "sinh_b", "cosh_b", "atan", "asin_b", "acos_b")  # the second row: primitives with an aux series
 BIN = ("add", "sub", "mul", "div_p", "addc", "mulc", "csub", "cdiv_p")
 
 
@@ -59,6 +60,20 @@ def ev(n, x, p, t, F):
             return a ** 2
         if k == "cube":
             return F.sin(a) ** 3
+        if k == "tan_b":
+            return F.tan(0.5 * F.sin(a))
+        if k == "tanh":
+            return F.tanh(F.sin(a))
+        if k == "sinh_b":
+            return F.sinh(F.cos(a))
+        if k == "cosh_b":
+            return F.cosh(F.sin(a))
+        if k == "atan":
+            return F.atan(a)
+        if k == "asin_b":
+            return F.asin(0.5 * F.sin(a))
+        if k == "acos_b":
+            return F.acos(0.5 * F.cos(a))
         return -a
     a, b, c = ev(n[1], x, p, t, F), ev(n[2], x, p, t, F), n[3]
     if k == "add":
@@ -81,7 +96,7 @@ def ev(n, x, p, t, F):
 def test_random_right_hand_sides_generic_equals_parsed_bitwise():
     rng = random.Random(20261105)
     order, checked, nops = 10, 0, 0
-    for case in range(40):
+    for case in range(60):
         dof = rng.choice((1, 2, 3))
         npar = rng.choice((0, 1, 2))
         trees = [gen(rng, dof, npar, rng.choice((2, 3, 4))) for _ in range(dof)]
@@ -100,4 +115,4 @@ def test_random_right_hand_sides_generic_equals_parsed_bitwise():
         assert np.array_equal(xg, xp), (case, trees)
         checked += 1
         nops += len(tape.ops)
-    assert checked == 40 and nops > 400  # a few hundred traced primitives went through both evaluators
+    assert checked == 60 and nops > 600  # a few hundred traced primitives went through both evaluators
